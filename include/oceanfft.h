@@ -1,0 +1,182 @@
+/*
+ * oceanfft.h -- C ABI of liboceanfft.so, the B200 (sm_100a) native plugin that replaces the
+ * spectral-ocean compute path of Mozobo/Ocean-Simulation behind WaterBody's surface.
+ *
+ * The reference has no FFI of its own: the path sits behind the C# class WaterBody and Unity's
+ * ComputeShader API.  Each entry point below therefore cites the WaterBody / IFFT member it
+ * stands in for (paths relative to the reference root):
+ *   WB      = Assets/Scripts/Water/WaterBody.cs
+ *   WC      = Assets/Scripts/Water/WaterCascade.cs
+ *   IFFT.cs = Assets/Scripts/Water/IFFT.cs
+ *   BO      = Assets/Scripts/Water/BuoyantObject.cs
+ *   IS/TD/FFT/RF = Assets/Shaders/Compute Shaders/Water/{InitialSpectrum,TimeDependentSpectrum,
+ *                  IFFT,ResultTexturesFiller}.compute
+ * INTEGRATION.md shows the C# [DllImport] shim (WaterBodyNative.cs) that binds them.
+ *
+ * Conventions
+ *   - plain C, POD structs, raw pointers and sizes; no CUDA or torch types cross the boundary
+ *     (device pointers and streams travel as void*).
+ *   - every function returns an OceanStatus (0 = OK) unless documented otherwise; the message
+ *     for the last failure on the calling thread is ocean_last_error().  Nothing throws.
+ *   - the library owns all device memory; callers own the host buffers they pass in.
+ *   - one CUDA stream per handle: calls on one handle must be externally serialised and take
+ *     effect in call order (Unity's in-order graphics queue, WB:180-193); different handles may
+ *     be driven from different threads.
+ *   - there is NO CPU fallback: without a CUDA device ocean_create fails with OCEAN_ERR_CUDA.
+ *
+ * Array layout (all outputs and all state): the reference's Texture2DArray layout flattened,
+ *   index = ((layer * N + y) * N + x) * channels, x fastest   (WB:206, IS:120 `uint3(id.xy, i)`).
+ */
+#ifndef OCEANFFT_H
+#define OCEANFFT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OCEAN_ABI_VERSION 1
+#define OCEAN_MAX_CASCADES 5 /* Water.shader:139 sizes its per-cascade arrays at 5 */
+#define OCEAN_MIN_SIZE 16
+#define OCEAN_MAX_SIZE 2048
+
+typedef enum OceanStatus {
+    OCEAN_OK = 0,
+    OCEAN_ERR_INVALID_ARGUMENT = 1, /* NULL pointer, bad enum, bad cascade index ... */
+    OCEAN_ERR_INVALID_SIZE = 2,     /* textureSize not a power of two in [16, 2048] */
+    OCEAN_ERR_INVALID_CASCADES = 3, /* nCascades outside [1, 5], wavelength <= 0, cutoffLow <= 0 ... */
+    OCEAN_ERR_INVALID_PARAMS = 4,   /* non-positive windSpeed / gravity / fetch / depth, zero wind vector */
+    OCEAN_ERR_CUDA = 5,             /* CUDA runtime failure (no device, out of memory, launch error) */
+    OCEAN_ERR_NOT_INITIALIZED = 6   /* ocean_step before ocean_init_spectrum */
+} OceanStatus;
+
+/* WaterBody's serialized ocean fields WB:10-14 + texturesSize WB:29 (uniforms WB:131-145).
+ * lambda is the horizontal-displacement (choppiness) scale.  The reference has none (it is
+ * hard-wired to 1: Water.shader:325-327, RF:27); parity is defined at lambda = 1. */
+typedef struct OceanParams {
+    float windSpeed; /* U10, m/s            WB:10 */
+    float windDirX;  /* unnormalised         WB:11 */
+    float windDirY;
+    float gravity;   /* m/s^2               WB:12 */
+    float fetch;     /* m                   WB:13 */
+    float depth;     /* m                   WB:14 */
+    int32_t textureSize; /* N               WB:29 */
+    float lambda;    /* 1.0 = reference */
+} OceanParams;
+
+/* WaterCascade WC:10-24 (flattened into 4 GPU buffers by WB:231-251). */
+typedef struct OceanCascade {
+    float wavelength; /* tile length L_i, m; dk = 2*PI/L_i   WC:10 */
+    float cutoffLow;  /* |k| >= cutoffLow                    WC:20 */
+    float cutoffHigh; /* |k| <= cutoffHigh                   WC:15 */
+    float swell;      /* WC:22 */
+    float fade;       /* WC:24 */
+} OceanCascade;
+
+typedef enum OceanArray {
+    OCEAN_DISPLACEMENT = 0, /* RGBA32F (Dx, Dy, Dz, 0)                  _DisplacementsTextures WB:278, RF:25 */
+    OCEAN_DERIVATIVES = 1,  /* RGBA32F (dDy/dx, dDy/dz, dDx/dx, dDz/dz) _DerivativesTextures   WB:279, RF:26 */
+    OCEAN_TURBULENCE = 2,   /* RGBA32F (foam x4)                        _TurbulenceTextures    WB:280, RF:28-32 */
+    OCEAN_INITIAL_SPECTRUM = 3, /* RGBA32F (h0(k), conj h0(-k))  initialSpectrumTextures WB:37, IS:120,141 */
+    OCEAN_WAVES_DATA = 4,       /* RGBA32F (kx, 1/|k|, kz, omega) wavesDataTextures      WB:38, IS:123 */
+    OCEAN_NOISE = 5,            /* RG32F, one layer, shared by all cascades      randomNoiseTexture WB:34 */
+    OCEAN_ROW_SPECTRA = 6       /* debug: state between the x and y passes, 2 planes of RGBA32F:
+                                   plane 0 = (DxDz, DyDxz), plane 1 = (DyxDyz, DxxDzz), each [layer][y][x] */
+} OceanArray;
+
+typedef enum OceanQueryMode {
+    OCEAN_QUERY_NEAREST_REF = 0,          /* WaterBody.GetWaterHeight WB:195-209, bit-exact, on the current frame */
+    OCEAN_QUERY_READBACK_REF = 1,         /* same lookup, but in the last completed readback: 0 until one exists (WB:197) */
+    OCEAN_QUERY_BILINEAR = 2,             /* extension: cascade 0, uv = world/wavelength[0] (Water.shader:325), bilinear, Repeat wrap */
+    OCEAN_QUERY_BILINEAR_ALL_CASCADES = 3 /* extension: sum over cascades, as the surface shader displaces vertices */
+} OceanQueryMode;
+
+typedef struct OceanHandle OceanHandle;     /* one WaterBody: C cascades of N x N on one device */
+typedef struct OceanEnsemble OceanEnsemble; /* pooled batch runner for many independent oceans */
+
+int ocean_abi_version(void);
+const char* ocean_last_error(void);
+int ocean_device_count(void); /* number of CUDA devices, 0 on failure */
+
+/* ---- lifetime: WaterBody.Awake WB:211-256 / OnDisable WB:300-309 ------------------------ */
+
+/* Allocates every array of WB:221-229 + IFFT.cs:36,51 on `device`, uploads or generates the
+ * noise texture (WB:86-100).  noiseRG: N*N*2 floats [y][x][2] on the host, or NULL to generate
+ * it on the device from `seed` (include/ocean_noise.h).  Does not compute the spectrum. */
+int ocean_create(const OceanParams* params, const OceanCascade* cascades, int nCascades,
+                 const float* noiseRG, uint64_t seed, int device, OceanHandle** out);
+void ocean_destroy(OceanHandle* h);
+
+/* Live parameter edit (the commented-out OnValidate WB:324-337).  textureSize must not change;
+ * cascades may be NULL to keep the current ones, otherwise nCascades must equal the handle's.
+ * Takes effect at the next ocean_init_spectrum. */
+int ocean_set_params(OceanHandle* h, const OceanParams* params, const OceanCascade* cascades, int nCascades);
+
+/* CalculateInitialSpectrumTextures WB:171-178: IS:99-129 then IS:135-143, one fused kernel. */
+int ocean_init_spectrum(OceanHandle* h);
+
+/* ---- per frame: WaterBody.CalculateWavesTexturesAtTime(float time) WB:180-193 ----------- */
+
+/* Enqueues one frame (TD:20-47 -> 4 x IFFT.cs:66-94 -> RF:16-34) on the handle's stream and
+ * advances the foam recursion by exactly one frame.  Asynchronous. */
+int ocean_step(OceanHandle* h, float time);
+int ocean_sync(OceanHandle* h); /* block until everything enqueued on the handle has finished */
+
+/* WaterBody.Update WB:284-297: ocean_step(time) + AsyncGPUReadback.Request of displacement
+ * layer 0 (WB:288) into library-owned pinned memory on a second stream.  The readback becomes
+ * visible to OCEAN_QUERY_READBACK_REF / ocean_readback_ptr once it has completed. */
+int ocean_update(OceanHandle* h, float time);
+/* Latest completed readback (N*N*4 floats, RGBA of displacement layer 0) or NULL; *frame gets
+ * the index of the frame it belongs to (-1 if none).  wait != 0 blocks for the newest request. */
+const float* ocean_readback_ptr(OceanHandle* h, int wait, int64_t* frame);
+
+/* ---- outputs: what WB:277-281 publishes to Water.shader ------------------------------------ */
+
+/* Device pointer + byte size of an array (owned by the handle, valid until ocean_destroy). */
+int ocean_get_output(OceanHandle* h, int which /*OceanArray*/, void** devPtr, size_t* bytes);
+/* Synchronous copy of one layer (cascade) to host memory; cascade = -1 copies all layers. */
+int ocean_copy_output(OceanHandle* h, int which /*OceanArray*/, int cascade, float* host);
+int ocean_get_wavelengths(OceanHandle* h, float* out /*[nCascades]*/, int* nCascades); /* _Wavelengths WB:281 */
+
+/* ---- foam state: the persistence implicit in the turbulence RenderTexture RF:28,32 --------- */
+int ocean_set_turbulence(OceanHandle* h, const float* host /* C*N*N*4 */);
+int ocean_reset_foam(OceanHandle* h);
+int64_t ocean_frame_index(OceanHandle* h); /* frames stepped since create / reset */
+
+/* ---- queries: WaterBody.GetWaterHeight(Vector3) WB:195-209, called from BO:18 -------------- */
+
+/* n points (x, z) -> n heights.  pointsOnDevice / heightsOnDevice select host or device buffers. */
+int ocean_query_heights(OceanHandle* h, const float* worldXZ, int n, int mode /*OceanQueryMode*/,
+                        float* heights, int pointsOnDevice, int heightsOnDevice);
+
+/* ---- plumbing ------------------------------------------------------------------------------ */
+int ocean_get_stream(OceanHandle* h, void** cudaStream);
+int ocean_set_stream(OceanHandle* h, void* cudaStream); /* share one stream between handles (NULL = own) */
+/* Kernel launches issued by this library on the calling thread's behalf since load (bench bookkeeping). */
+uint64_t ocean_launch_count(void);
+/* Names of the most recent launch configuration, for DESIGN.md / bench: writes a short text. */
+int ocean_describe(OceanHandle* h, char* buf, size_t bufBytes);
+
+/* ---- ensembles: many independent oceans (BASELINE config 5) -------------------------------- */
+
+/* A pooled runner for `batch` oceans of (N, nCascades) at a time on one device.  Every state
+ * shares the cascade set; ocean parameters and the noise seed vary per state. */
+int ocean_ensemble_create(int textureSize, const OceanCascade* cascades, int nCascades, int batch,
+                          int device, OceanEnsemble** out);
+void ocean_ensemble_destroy(OceanEnsemble* e);
+/* For each state s in [0, nStates): noise(seed[s]) -> init spectrum -> one frame at `time` from
+ * zero turbulence -> 64-bit checksum of the three output arrays (sum of the fp32 bit patterns).
+ * Processes the states in waves of `batch`.  checksums: nStates x 3 uint64 on the host.
+ * Asynchronous work is drained before returning. */
+int ocean_ensemble_run(OceanEnsemble* e, const OceanParams* states, const uint64_t* seeds, int nStates,
+                       float time, uint64_t* checksums);
+/* Device pointers of the pooled output arrays of the last wave ([batch*C][N][N][4]). */
+int ocean_ensemble_get_output(OceanEnsemble* e, int which, void** devPtr, size_t* bytes);
+int ocean_ensemble_copy_output(OceanEnsemble* e, int which, int slot, float* host /* C*N*N*4 */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OCEANFFT_H */

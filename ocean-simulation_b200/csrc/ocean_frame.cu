@@ -1,0 +1,321 @@
+// ocean_frame.cu -- the per-frame hot path: two kernels per frame instead of the reference's
+// 1 + 4*(2*log2 N + 1) + 1 dispatches (WB:180-193, IFFT.cs:66-94).
+//
+//   ocean_rows_kernel  = CalculateTimeDependentComplexAmplitudesAndDerivatives (TD:20-47)
+//                        fused into the x-direction inverse FFT of all four packed spectra
+//                        (HorizontalStepIFFT x log2 N, FFT:48-57).
+//   ocean_cols_kernel  = the y-direction inverse FFT (VerticalStepIFFT x log2 N, FFT:60-69)
+//                        fused with Permute (FFT:73-78) and FillResultTextures (RF:16-34):
+//                        (-1)^(x+y), unpack, lambda, Jacobian, foam recursion, 128-bit stores.
+//
+// Bytes per texel-cascade: rows read h0 16 + waveData 16 and write 32 of intermediate; cols
+// read that 32 (L2-resident) + turbulence 16 and write 3 x 16.  Algorithmic = 96 B.
+// Bandwidth-bound fp32 FFT: tensor cores are not used (no dense contraction here).
+#include <stdio.h>
+
+#include "ocean_fft.cuh"
+#include "ocean_internal.h"
+
+namespace ocean {
+
+// Streaming (read-once / write-once) accesses keep the intermediate resident in L2.
+__device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
+__device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
+
+template <int N> struct RowCfg {
+    static constexpr int T = N / 8;
+    static constexpr int R = (T >= 64) ? 1 : 64 / T;  // rows per CTA: CTA >= 64 threads
+    static constexpr int THREADS = R * T;
+    static constexpr bool DB = (N != 512);            // N=512: single buffer so 14 CTAs fit per SM
+    static constexpr int MINB = (N == 512) ? 14 : 1;
+    using FFT = LineFFT<N, R, false, DB>;
+};
+
+template <int N> struct ColCfg {
+    static constexpr int T = N / 8;
+    static constexpr int W = (T >= 64) ? 2 : ((T >= 32) ? 4 : 8);  // adjacent columns per CTA
+    static constexpr int THREADS = W * T;
+    static constexpr bool DB = (N != 512);
+    static constexpr int MINB = (N == 512) ? 7 : 1;
+    using FFT = LineFFT<N, W, true, DB>;
+};
+
+// ---------------------------------------------------------------------------------------------
+template <int N>
+__global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_rows_kernel(const FrameArgs a) {
+    using Cfg = RowCfg<N>;
+    using FFT = typename Cfg::FFT;
+    constexpr int T = Cfg::T;
+    extern __shared__ float4 smem[];
+    const int tid = threadIdx.x & (T - 1);
+    const int row = threadIdx.x / T;
+    const size_t totalRows = (size_t)a.layers * N;
+    size_t line = (size_t)blockIdx.x * Cfg::R + row;  // = layer*N + y
+    const bool active = line < totalRows;
+    if (!active) line = totalRows - 1;  // keep every thread in the barriers; results are dropped
+    const float4* __restrict__ H = a.h0 + line * N;
+    const float4* __restrict__ Wd = a.wave + line * N;
+    const float time = a.time;
+
+    float4 pa[8], pb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 h0 = ld_stream(H + tid + T * j);
+        const float4 wv = ld_stream(Wd + tid + T * j);
+        // TD:23-26
+        float sn, cs;
+        sincosf(wv.w * time, &sn, &cs);
+        const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
+        const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
+        const float ihx = -hy, ihy = hx;
+        const float kx = wv.x, ik = wv.y, kz = wv.z;
+        // TD:29-40
+        const float ydx_x = ihx * kx, ydx_y = ihy * kx;
+        const float ydz_x = ihx * kz, ydz_y = ihy * kz;
+        const float X_x = ydx_x * ik, X_y = ydx_y * ik;
+        const float Z_x = ydz_x * ik, Z_y = ydz_y * ik;
+        const float ax = -hx * ik, ay = -hy * ik;
+        const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
+        const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
+        const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
+        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz)
+        pa[j] = make_float4(X_x - Z_y, X_y + Z_x, hx - zdx_y, hy + zdx_x);
+        pb[j] = make_float4(ydx_x - ydz_y, ydx_y + ydz_x, xdx_x - zdz_y, xdx_y + zdz_x);
+    }
+
+    FFT::run(pa, smem, tid, row, a.twiddle, 0);
+    if (active) {
+        float4* __restrict__ out = a.rowsA + line * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out[tid + T * j] = pa[j];
+    }
+    FFT::run(pb, smem, tid, row, a.twiddle, FFT::EXCHANGES);
+    if (active) {
+        float4* __restrict__ out = a.rowsB + line * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out[tid + T * j] = pb[j];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int N>
+__global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_cols_kernel(const FrameArgs a) {
+    using Cfg = ColCfg<N>;
+    using FFT = typename Cfg::FFT;
+    constexpr int T = Cfg::T, W = Cfg::W;
+    extern __shared__ float4 smem[];
+    const int xw = threadIdx.x & (W - 1);
+    const int tid = threadIdx.x / W;
+    const int x = blockIdx.x * W + xw;
+    const size_t base = (size_t)blockIdx.y * N * N + x;  // texel (x, 0) of this layer
+    const float lambda = a.lambda;
+    // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
+    const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
+
+    float4 r[8];
+    float dxz[8];
+    {
+        const float4* __restrict__ in = a.rowsA + base;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = __ldcg(in + (size_t)(tid + T * j) * N);
+    }
+    FFT::run(r, smem, tid, xw, a.twiddle, 0);
+    {
+        float4* __restrict__ disp = a.disp + base;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            // r = (DxDz, DyDxz) * sign;  displacement = (Dx, Dy, Dz)  RF:25 (alpha := 0)
+            const float dx = r[j].x * sgn, dz = r[j].y * sgn, dy = r[j].z * sgn;
+            dxz[j] = r[j].w * sgn * lambda;
+            st_stream(disp + (size_t)(tid + T * j) * N, make_float4(dx * lambda, dy, dz * lambda, 0.0f));
+        }
+    }
+    {
+        const float4* __restrict__ in = a.rowsB + base;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = __ldcg(in + (size_t)(tid + T * j) * N);
+    }
+    FFT::run(r, smem, tid, xw, a.twiddle, FFT::EXCHANGES);
+    {
+        float4* __restrict__ deriv = a.deriv + base;
+        float4* __restrict__ turb = a.turb + base;
+        const float decay = a.foamDecay;
+        const bool zeroFoam = a.zeroFoam != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const size_t o = (size_t)(tid + T * j) * N;
+            // r = (DyxDyz, DxxDzz) * sign;  derivatives RF:26
+            const float dyx = r[j].x * sgn, dyz = r[j].y * sgn;
+            const float dxx = r[j].z * sgn * lambda, dzz = r[j].w * sgn * lambda;
+            st_stream(deriv + o, make_float4(dyx, dyz, dxx, dzz));
+            // RF:27-32
+            const float jac = (1.0f + dxx) * (1.0f + dzz) - dxz[j] * dxz[j];
+            float foam = zeroFoam ? 0.0f : ld_stream(turb + o).x;
+            foam *= decay;
+            if (foam < jac) foam += jac;
+            st_stream(turb + o, make_float4(foam, foam, foam, foam));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// WaterBody.GetWaterHeight WB:195-209 (mode 0), plus bilinear extensions at the shader's own
+// mapping uv = worldXZ / wavelength (Water.shader:325) with Repeat wrap.
+struct QueryArgs {
+    const float4* disp;
+    const float2* pts;
+    float* out;
+    int N, C, n, mode;
+    float wavelengths[OCEAN_MAX_CASCADES];
+};
+
+__device__ __forceinline__ float bilinear_height(const float4* __restrict__ layer, int N, float u, float v) {
+    // texel centres at (i + 0.5)/N, Repeat wrap
+    const float fx = u * (float)N - 0.5f, fy = v * (float)N - 0.5f;
+    const float x0f = floorf(fx), y0f = floorf(fy);
+    const float wx = fx - x0f, wy = fy - y0f;
+    const int x0 = ((int)x0f) & (N - 1), y0 = ((int)y0f) & (N - 1);
+    const int x1 = (x0 + 1) & (N - 1), y1 = (y0 + 1) & (N - 1);
+    const float h00 = __ldg(&layer[(size_t)y0 * N + x0]).y, h10 = __ldg(&layer[(size_t)y0 * N + x1]).y;
+    const float h01 = __ldg(&layer[(size_t)y1 * N + x0]).y, h11 = __ldg(&layer[(size_t)y1 * N + x1]).y;
+    const float a = h00 + (h10 - h00) * wx, b = h01 + (h11 - h01) * wx;
+    return a + (b - a) * wy;
+}
+
+__global__ void ocean_query_kernel(const QueryArgs q) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q.n) return;
+    const float2 p = q.pts[i];
+    const int N = q.N;
+    if (q.mode == OCEAN_QUERY_NEAREST_REF) {
+        // Mathf.InverseLerp(-N/2, N/2, v) = Clamp01((v - a) / (b - a))   WB:199-200
+        const float lo = (float)(-(N / 2)), hi = (float)(N / 2);
+        float u = __fdiv_rn(__fsub_rn(p.x, lo), __fsub_rn(hi, lo));
+        float v = __fdiv_rn(__fsub_rn(p.y, lo), __fsub_rn(hi, lo));
+        u = fminf(fmaxf(u, 0.0f), 1.0f);
+        v = fminf(fmaxf(v, 0.0f), 1.0f);
+        int x = (int)__fmul_rn(u, (float)N), y = (int)__fmul_rn(v, (float)N);  // WB:203-204
+        x = min(max(x, 0), N - 1);
+        y = min(max(y, 0), N - 1);
+        q.out[i] = __ldg(&q.disp[(size_t)y * N + x]).y;  // .g of layer 0  WB:206-208
+        return;
+    }
+    const int nc = (q.mode == OCEAN_QUERY_BILINEAR_ALL_CASCADES) ? q.C : 1;
+    float h = 0.0f;
+    for (int c = 0; c < nc; ++c) {
+        const float inv = 1.0f / q.wavelengths[c];
+        float u = p.x * inv, v = p.y * inv;
+        u -= floorf(u);
+        v -= floorf(v);
+        h += bilinear_height(q.disp + (size_t)c * N * N, N, u, v);
+    }
+    q.out[i] = h;
+}
+
+// 64-bit sum of the fp32 bit patterns of one state's array (order-independent => deterministic)
+__global__ void ocean_checksum_kernel(const uint4* __restrict__ arr, size_t float4PerState, unsigned long long* out,
+                                      int outStride) {
+    const uint4* base = arr + (size_t)blockIdx.y * float4PerState;
+    unsigned long long acc = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < float4PerState; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = base[i];
+        acc += (unsigned long long)v.x + v.y + v.z + v.w;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out + (size_t)blockIdx.y * outStride, acc);
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t s) {
+    using Cfg = RowCfg<N>;
+    const size_t totalRows = (size_t)a.layers * N;
+    const unsigned grid = (unsigned)((totalRows + Cfg::R - 1) / Cfg::R);
+    ocean_rows_kernel<N><<<grid, Cfg::THREADS, Cfg::FFT::SMEM_BYTES, s>>>(a);
+    count_launch();
+    return cudaGetLastError();
+}
+template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t s) {
+    using Cfg = ColCfg<N>;
+    dim3 grid(N / Cfg::W, a.layers);
+    ocean_cols_kernel<N><<<grid, Cfg::THREADS, Cfg::FFT::SMEM_BYTES, s>>>(a);
+    count_launch();
+    return cudaGetLastError();
+}
+template <int N> static cudaError_t configure() {
+    cudaError_t e = cudaFuncSetAttribute(ocean_rows_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, RowCfg<N>::FFT::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(ocean_cols_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColCfg<N>::FFT::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    // prefer the largest shared-memory carve-out: occupancy is set by registers and smem, not L1
+    cudaFuncSetAttribute(ocean_rows_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(ocean_cols_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaSuccess;
+}
+template <int N> static const char* describe() {
+    static char buf[256];
+    snprintf(buf, sizeof buf,
+             "rows<N=%d>: %d rows/CTA, %d threads, %d B smem, %s buffer; cols<N=%d>: %d columns/CTA, %d threads, %d B smem, %s buffer",
+             N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::FFT::SMEM_BYTES, RowCfg<N>::DB ? "double" : "single", N,
+             ColCfg<N>::W, ColCfg<N>::THREADS, ColCfg<N>::FFT::SMEM_BYTES, ColCfg<N>::DB ? "double" : "single");
+    return buf;
+}
+
+#define OCEAN_DISPATCH_N(N_, CALL)                 \
+    switch (N_) {                                  \
+        case 16: return CALL(16);                  \
+        case 32: return CALL(32);                  \
+        case 64: return CALL(64);                  \
+        case 128: return CALL(128);                \
+        case 256: return CALL(256);                \
+        case 512: return CALL(512);                \
+        case 1024: return CALL(1024);              \
+        case 2048: return CALL(2048);              \
+        default: break;                            \
+    }
+
+cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s) {
+#define CALL(n) rows_launch<n>(a, s)
+    OCEAN_DISPATCH_N(a.N, CALL)
+#undef CALL
+    return cudaErrorInvalidValue;
+}
+cudaError_t launch_cols(const FrameArgs& a, cudaStream_t s) {
+#define CALL(n) cols_launch<n>(a, s)
+    OCEAN_DISPATCH_N(a.N, CALL)
+#undef CALL
+    return cudaErrorInvalidValue;
+}
+cudaError_t configure_frame_kernels(int N) {
+#define CALL(n) configure<n>()
+    OCEAN_DISPATCH_N(N, CALL)
+#undef CALL
+    return cudaErrorInvalidValue;
+}
+const char* describe_frame_kernels(int N) {
+#define CALL(n) describe<n>()
+    OCEAN_DISPATCH_N(N, CALL)
+#undef CALL
+    return "unsupported N";
+}
+
+cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths, const float2* pts, float* out, int n,
+                         int mode, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    QueryArgs q;
+    q.disp = disp; q.pts = pts; q.out = out; q.N = N; q.C = C; q.n = n; q.mode = mode;
+    for (int i = 0; i < OCEAN_MAX_CASCADES; ++i) q.wavelengths[i] = i < C ? wavelengths[i] : 1.0f;
+    ocean_query_kernel<<<(n + 255) / 256, 256, 0, s>>>(q);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out, int outStride,
+                            cudaStream_t s) {
+    dim3 grid(64, nStates);
+    ocean_checksum_kernel<<<grid, 256, 0, s>>>((const uint4*)arr, float4PerState, out, outStride);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace ocean

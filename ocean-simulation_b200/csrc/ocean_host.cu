@@ -1,0 +1,746 @@
+// ocean_host.cu -- host side of liboceanfft.so: the C++ mirror of WaterBody (WB) / IFFT (IFFT.cs)
+// and the C ABI declared in include/oceanfft.h.  The reference's host is C# (no toolchain in
+// this image), so the host logic is C++ with the same member names and call order.
+//
+//   WaterBodyNative::Awake                        <- WaterBody.Awake WB:211-256
+//   WaterBodyNative::CalculateInitialSpectrumTextures <- WB:171-178
+//   WaterBodyNative::CalculateWavesTexturesAtTime <- WB:180-193
+//   WaterBodyNative::Update                       <- WB:284-297
+//   WaterBodyNative::GetWaterHeight (batched)     <- WB:195-209
+//   WaterBodyNative::OnDisable                    <- WB:300-309
+//
+// There is no CPU implementation of any kernel here: if CUDA is unavailable every entry point
+// that needs the device fails with OCEAN_ERR_CUDA.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ocean_internal.h"
+
+namespace ocean {
+
+static std::atomic<uint64_t> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+uint64_t launch_count() { return g_launches.load(std::memory_order_relaxed); }
+
+static thread_local std::string g_error;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define OCEAN_CUDA(expr)                                                                             \
+    do {                                                                                             \
+        cudaError_t e__ = (expr);                                                                    \
+        if (e__ != cudaSuccess)                                                                      \
+            return fail(OCEAN_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+struct DeviceScope {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceScope(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceScope() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+static bool finite_pos(float v) { return std::isfinite(v) && v > 0.0f; }
+
+static int validate_params(const OceanParams& p) {
+    const int N = p.textureSize;
+    if (N < OCEAN_MIN_SIZE || N > OCEAN_MAX_SIZE || (N & (N - 1)) != 0)
+        return fail(OCEAN_ERR_INVALID_SIZE, "textureSize %d is not a power of two in [%d, %d]", N, OCEAN_MIN_SIZE, OCEAN_MAX_SIZE);
+    if (!finite_pos(p.windSpeed) || !finite_pos(p.gravity) || !finite_pos(p.fetch) || !finite_pos(p.depth))
+        return fail(OCEAN_ERR_INVALID_PARAMS, "windSpeed, gravity, fetch and depth must be finite and > 0");
+    if (!std::isfinite(p.windDirX) || !std::isfinite(p.windDirY) || (p.windDirX == 0.0f && p.windDirY == 0.0f))
+        return fail(OCEAN_ERR_INVALID_PARAMS, "wind direction must be a finite non-zero vector");
+    if (!std::isfinite(p.lambda)) return fail(OCEAN_ERR_INVALID_PARAMS, "lambda must be finite");
+    return OCEAN_OK;
+}
+
+static int validate_cascades(const OceanCascade* c, int n) {
+    if (n < 1 || n > OCEAN_MAX_CASCADES) return fail(OCEAN_ERR_INVALID_CASCADES, "nCascades %d outside [1, %d]", n, OCEAN_MAX_CASCADES);
+    if (!c) return fail(OCEAN_ERR_INVALID_ARGUMENT, "cascades is NULL");
+    for (int i = 0; i < n; ++i) {
+        if (!finite_pos(c[i].wavelength)) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade %d: wavelength must be > 0", i);
+        if (!finite_pos(c[i].cutoffLow)) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade %d: cutoffLow must be > 0 (k = 0 gives NaN, IS:114-120)", i);
+        if (!(c[i].cutoffHigh > 0.0f)) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade %d: cutoffHigh must be > 0", i);
+        if (!std::isfinite(c[i].swell) || !std::isfinite(c[i].fade)) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade %d: swell/fade must be finite", i);
+    }
+    return OCEAN_OK;
+}
+
+// fp32, reference operation order (this file is compiled with -ffp-contract=off on the host)
+static const float kPI = 3.14159265f;  // IS:8
+
+static StateConsts make_state_consts(const OceanParams& p) {
+    StateConsts s;
+    const float U = p.windSpeed, g = p.gravity, F = p.fetch, D = p.depth;
+    s.windSpeed = U; s.gravity = g; s.fetch = F; s.depth = D;
+    s.sqrtDepthOverG = sqrtf(D / g);                                        // IS:39
+    s.peakOmega = 22.0f * powf(fabsf(g * g / (U * F)), 0.3333f);            // IS:118
+    s.alpha = 0.076f * powf(fabsf(U * U / (F * g)), 0.22f);                 // IS:48
+    const float peakSpeed = g / s.peakOmega;                                // IS:63
+    s.mu = -2.33f - 1.45f * (U / peakSpeed - 1.17f);                        // IS:64
+    const float len = sqrtf(p.windDirX * p.windDirX + p.windDirY * p.windDirY);
+    s.windTheta = atan2f(p.windDirY / len, p.windDirX / len);               // IS:80-81
+    s.lambda = p.lambda;
+    s.pad0 = s.pad1 = 0.0f;
+    return s;
+}
+
+static SpreadConsts make_spread_consts() {
+    SpreadConsts c;
+    c.pi = kPI;
+    c.c2 = powf(logf(2.0f), 2.0f) / kPI - kPI / 12.0f;  // IS:72
+    c.c1 = logf(2.0f) / kPI;
+    c.c0 = 1.0f / (2.0f * kPI);
+    c.twoSqrtPi = 2.0f * sqrtf(kPI);                    // IS:73
+    return c;
+}
+
+static CascadeConsts make_cascade_consts(const OceanCascade& c) {
+    CascadeConsts k;
+    k.dk = 2.0f * kPI / c.wavelength;  // IS:110
+    k.cutoffLow = c.cutoffLow; k.cutoffHigh = c.cutoffHigh; k.swell = c.swell; k.fade = c.fade;
+    k.wavelength = c.wavelength;
+    return k;
+}
+
+// e^{+2 pi i j / N}: the table the radix-8 stages index (replaces the butterfly texture of
+// IFFT.cs:36 / FFT:37-45).  Evaluated in double, rounded once.
+static std::vector<float2> make_twiddles(int N) {
+    std::vector<float2> t(N);
+    for (int j = 0; j < N; ++j) {
+        const double a = 2.0 * M_PI * (double)j / (double)N;
+        t[j] = make_float2((float)cos(a), (float)sin(a));
+    }
+    return t;
+}
+
+}  // namespace ocean
+
+using namespace ocean;
+
+// ---------------------------------------------------------------------------------------------
+// WaterBodyNative: one WaterBody on one device.
+struct OceanHandle {
+    int device = 0;
+    int N = 0, C = 0;
+    OceanParams params{};
+    OceanCascade cascades[OCEAN_MAX_CASCADES]{};
+    cudaStream_t ownStream = nullptr, stream = nullptr, copyStream = nullptr;
+    // arrays of WB:221-229 (+ noise WB:34); rowsA/rowsB replace the 4 spectra + ping-pong array
+    float2* noise = nullptr;
+    float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr;
+    float4 *disp = nullptr, *deriv = nullptr, *turb = nullptr;
+    float2* twiddle = nullptr;
+    StateConsts* stateDev = nullptr;
+    uint64_t* seedDev = nullptr;
+    bool spectrumReady = false;
+    bool foamZero = true;
+    int64_t frame = 0;
+    // AsyncGPUReadback of displacement layer 0 (WB:288-296), triple buffered: one slot is the
+    // visible buoyancyData (WB:58), up to two are in flight
+    static constexpr int RB = 3;
+    float4* rbStage[RB] = {nullptr, nullptr, nullptr};
+    float* rbHost[RB] = {nullptr, nullptr, nullptr};
+    cudaEvent_t rbDone[RB] = {nullptr, nullptr, nullptr};
+    cudaEvent_t rbSnap = nullptr;
+    int64_t rbFrame[RB] = {-1, -1, -1};
+    bool rbPending[RB] = {false, false, false};
+    int rbLatest = -1;  // slot of the newest completed readback
+    // query scratch
+    float2* qPts = nullptr;
+    float* qOut = nullptr;
+    int qCap = 0;
+
+    size_t texels() const { return (size_t)N * N; }
+    size_t layerBytes4() const { return texels() * sizeof(float4); }
+
+    int Awake(const float* noiseHost, uint64_t seed);
+    int CalculateInitialSpectrumTextures();
+    int CalculateWavesTexturesAtTime(float time);
+    int Update(float time);
+    void PollReadbacks(bool wait);
+    int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
+    void OnDisable();
+};
+
+int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
+    const size_t t = texels();
+    OCEAN_CUDA(cudaStreamCreateWithFlags(&ownStream, cudaStreamNonBlocking));
+    OCEAN_CUDA(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking));
+    stream = ownStream;
+    OCEAN_CUDA(cudaMalloc(&noise, t * sizeof(float2)));
+    OCEAN_CUDA(cudaMalloc(&h0, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&wave, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&rowsA, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&rowsB, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&disp, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&deriv, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&turb, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&twiddle, N * sizeof(float2)));
+    OCEAN_CUDA(cudaMalloc(&stateDev, sizeof(StateConsts)));
+    OCEAN_CUDA(cudaMalloc(&seedDev, sizeof(uint64_t)));
+    OCEAN_CUDA(cudaMemsetAsync(disp, 0, C * t * sizeof(float4), stream));
+    OCEAN_CUDA(cudaMemsetAsync(deriv, 0, C * t * sizeof(float4), stream));
+    OCEAN_CUDA(cudaMemsetAsync(turb, 0, C * t * sizeof(float4), stream));  // fresh RenderTexture
+    const std::vector<float2> tw = make_twiddles(N);
+    OCEAN_CUDA(cudaMemcpyAsync(twiddle, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice, stream));
+    if (noiseHost) {  // GenerateRandomNoiseTexture WB:86-100: the caller supplies the texture
+        OCEAN_CUDA(cudaMemcpyAsync(noise, noiseHost, t * sizeof(float2), cudaMemcpyHostToDevice, stream));
+    } else {          // ... or it is generated on the device from the seed
+        OCEAN_CUDA(cudaMemcpyAsync(seedDev, &seed, sizeof seed, cudaMemcpyHostToDevice, stream));
+        OCEAN_CUDA(launch_noise(seedDev, 1, N, noise, stream));
+    }
+    OCEAN_CUDA(configure_frame_kernels(N));
+    for (int i = 0; i < RB; ++i) {
+        OCEAN_CUDA(cudaMalloc(&rbStage[i], layerBytes4()));
+        OCEAN_CUDA(cudaMallocHost(&rbHost[i], layerBytes4()));
+        OCEAN_CUDA(cudaEventCreateWithFlags(&rbDone[i], cudaEventDisableTiming));
+    }
+    OCEAN_CUDA(cudaEventCreateWithFlags(&rbSnap, cudaEventDisableTiming));
+    OCEAN_CUDA(cudaStreamSynchronize(stream));  // host staging (tw, seed) may go out of scope
+    return OCEAN_OK;
+}
+
+int OceanHandle::CalculateInitialSpectrumTextures() {
+    const StateConsts sc = make_state_consts(params);
+    OCEAN_CUDA(cudaMemcpyAsync(stateDev, &sc, sizeof sc, cudaMemcpyHostToDevice, stream));
+    InitArgs a{};
+    a.N = N; a.C = C; a.nStates = 1;
+    a.sc = make_spread_consts();
+    for (int i = 0; i < C; ++i) a.casc[i] = make_cascade_consts(cascades[i]);
+    a.states = stateDev; a.noise = noise; a.h0 = h0; a.wave = wave;
+    OCEAN_CUDA(launch_init(a, stream));
+    OCEAN_CUDA(cudaStreamSynchronize(stream));  // `sc` is stack memory
+    spectrumReady = true;
+    return OCEAN_OK;
+}
+
+int OceanHandle::CalculateWavesTexturesAtTime(float time) {
+    if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_step before ocean_init_spectrum");
+    FrameArgs a{};
+    a.N = N; a.layers = C;
+    a.h0 = h0; a.wave = wave; a.rowsA = rowsA; a.rowsB = rowsB;
+    a.disp = disp; a.deriv = deriv; a.turb = turb; a.twiddle = twiddle;
+    a.time = time; a.lambda = params.lambda;
+    a.foamDecay = expf(-2.0f);  // RF:29-30
+    a.zeroFoam = foamZero ? 1 : 0;
+    OCEAN_CUDA(launch_rows(a, stream));
+    OCEAN_CUDA(launch_cols(a, stream));
+    foamZero = false;
+    ++frame;
+    return OCEAN_OK;
+}
+
+void OceanHandle::PollReadbacks(bool wait) {
+    for (int i = 0; i < RB; ++i) {
+        if (!rbPending[i]) continue;
+        cudaError_t e = wait ? cudaEventSynchronize(rbDone[i]) : cudaEventQuery(rbDone[i]);
+        if (e == cudaSuccess) {
+            rbPending[i] = false;
+            if (rbLatest < 0 || rbFrame[i] > rbFrame[rbLatest]) rbLatest = i;
+        } else if (e == cudaErrorNotReady) {
+            cudaGetLastError();
+        }
+    }
+}
+
+int OceanHandle::Update(float time) {
+    int rc = CalculateWavesTexturesAtTime(time);
+    if (rc != OCEAN_OK) return rc;
+    // pick a slot that is neither in flight nor the visible buoyancyData
+    int s = -1;
+    for (;;) {
+        PollReadbacks(false);
+        for (int i = 0; i < RB && s < 0; ++i)
+            if (!rbPending[i] && i != rbLatest) s = i;
+        if (s >= 0) break;
+        int oldest = -1;
+        for (int i = 0; i < RB; ++i)
+            if (rbPending[i] && (oldest < 0 || rbFrame[i] < rbFrame[oldest])) oldest = i;
+        OCEAN_CUDA(cudaEventSynchronize(rbDone[oldest]));
+    }
+    // snapshot layer 0 on the compute stream, ship it to the host on the copy stream
+    OCEAN_CUDA(cudaMemcpyAsync(rbStage[s], disp, layerBytes4(), cudaMemcpyDeviceToDevice, stream));
+    OCEAN_CUDA(cudaEventRecord(rbSnap, stream));
+    OCEAN_CUDA(cudaStreamWaitEvent(copyStream, rbSnap, 0));
+    OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], layerBytes4(), cudaMemcpyDeviceToHost, copyStream));
+    OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
+    rbFrame[s] = frame - 1;
+    rbPending[s] = true;
+    return OCEAN_OK;
+}
+
+int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev) {
+    if (n == 0) return OCEAN_OK;
+    if (mode == OCEAN_QUERY_READBACK_REF) {
+        // WB:195-209 verbatim semantics: a host lookup into buoyancyData, the last completed
+        // AsyncGPUReadback; returns 0 until one exists (WB:197).  Host buffers only.
+        if (ptsDev || outDev) return fail(OCEAN_ERR_INVALID_ARGUMENT, "READBACK_REF works on host buffers");
+        PollReadbacks(false);
+        const float* data = rbLatest >= 0 ? rbHost[rbLatest] : nullptr;
+        for (int i = 0; i < n; ++i) {
+            if (!data) { heights[i] = 0.0f; continue; }
+            const float lo = (float)(-(N / 2)), hi = (float)(N / 2);
+            float u = (worldXZ[2 * i] - lo) / (hi - lo), v = (worldXZ[2 * i + 1] - lo) / (hi - lo);
+            u = u < 0.0f ? 0.0f : (u > 1.0f ? 1.0f : u);
+            v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+            int x = (int)(u * (float)N), y = (int)(v * (float)N);
+            x = x < 0 ? 0 : (x > N - 1 ? N - 1 : x);
+            y = y < 0 ? 0 : (y > N - 1 ? N - 1 : y);
+            heights[i] = data[((size_t)y * N + x) * 4 + 1];
+        }
+        return OCEAN_OK;
+    }
+    if (n > qCap && (!ptsDev || !outDev)) {
+        if (qPts) cudaFree(qPts);
+        if (qOut) cudaFree(qOut);
+        qPts = nullptr; qOut = nullptr; qCap = 0;
+        OCEAN_CUDA(cudaMalloc(&qPts, (size_t)n * sizeof(float2)));
+        OCEAN_CUDA(cudaMalloc(&qOut, (size_t)n * sizeof(float)));
+        qCap = n;
+    }
+    const float2* pts = (const float2*)worldXZ;
+    if (!ptsDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(qPts, worldXZ, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, stream));
+        pts = qPts;
+    }
+    float* out = outDev ? heights : qOut;
+    float wl[OCEAN_MAX_CASCADES];
+    for (int i = 0; i < C; ++i) wl[i] = cascades[i].wavelength;
+    OCEAN_CUDA(launch_query(disp, N, C, wl, pts, out, n, mode, stream));
+    if (!outDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(heights, qOut, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+        OCEAN_CUDA(cudaStreamSynchronize(stream));
+    } else if (!ptsDev) {
+        OCEAN_CUDA(cudaStreamSynchronize(stream));  // the caller may reuse its host points
+    }
+    return OCEAN_OK;
+}
+
+void OceanHandle::OnDisable() {
+    if (stream) cudaStreamSynchronize(stream);
+    if (copyStream) cudaStreamSynchronize(copyStream);
+    void* dev[] = {noise, h0, wave, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
+    for (void* p : dev)
+        if (p) cudaFree(p);
+    for (int i = 0; i < RB; ++i) {
+        if (rbHost[i]) cudaFreeHost(rbHost[i]);
+        if (rbDone[i]) cudaEventDestroy(rbDone[i]);
+    }
+    if (rbSnap) cudaEventDestroy(rbSnap);
+    if (ownStream) cudaStreamDestroy(ownStream);
+    if (copyStream) cudaStreamDestroy(copyStream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Ensemble runner: waves of `batch` independent oceans through pooled buffers.
+struct OceanEnsemble {
+    int device = 0, N = 0, C = 0, batch = 0;
+    OceanCascade cascades[OCEAN_MAX_CASCADES]{};
+    cudaStream_t stream = nullptr;
+    float2* noise = nullptr;
+    float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
+    float2* twiddle = nullptr;
+    // double-buffered parameter / result staging so consecutive waves overlap
+    StateConsts* stateDev[2] = {nullptr, nullptr};
+    uint64_t* seedDev[2] = {nullptr, nullptr};
+    unsigned long long* sumDev[2] = {nullptr, nullptr};
+    StateConsts* stateHost[2] = {nullptr, nullptr};
+    uint64_t* seedHost[2] = {nullptr, nullptr};
+    unsigned long long* sumHost[2] = {nullptr, nullptr};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    int lastCount = 0;
+
+    size_t stateFloat4() const { return (size_t)C * N * N; }
+    int create();
+    int run(const OceanParams* states, const uint64_t* seeds, int nStates, float time, uint64_t* checksums);
+    void destroy();
+};
+
+int OceanEnsemble::create() {
+    const size_t t = (size_t)N * N;
+    OCEAN_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    OCEAN_CUDA(cudaMalloc(&noise, batch * t * sizeof(float2)));
+    float4** arrs[] = {&h0, &wave, &rowsA, &rowsB, &disp, &deriv, &turb};
+    for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&twiddle, N * sizeof(float2)));
+    const std::vector<float2> tw = make_twiddles(N);
+    OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice));
+    for (int i = 0; i < 2; ++i) {
+        OCEAN_CUDA(cudaMalloc(&stateDev[i], batch * sizeof(StateConsts)));
+        OCEAN_CUDA(cudaMalloc(&seedDev[i], batch * sizeof(uint64_t)));
+        OCEAN_CUDA(cudaMalloc(&sumDev[i], (size_t)batch * 3 * sizeof(unsigned long long)));
+        OCEAN_CUDA(cudaMallocHost(&stateHost[i], batch * sizeof(StateConsts)));
+        OCEAN_CUDA(cudaMallocHost(&seedHost[i], batch * sizeof(uint64_t)));
+        OCEAN_CUDA(cudaMallocHost(&sumHost[i], (size_t)batch * 3 * sizeof(unsigned long long)));
+        OCEAN_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+    }
+    OCEAN_CUDA(configure_frame_kernels(N));
+    return OCEAN_OK;
+}
+
+int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nStates, float time, uint64_t* checksums) {
+    InitArgs ia{};
+    ia.N = N; ia.C = C;
+    ia.sc = make_spread_consts();
+    for (int i = 0; i < C; ++i) ia.casc[i] = make_cascade_consts(cascades[i]);
+    ia.noise = noise; ia.h0 = h0; ia.wave = wave;
+    int waveIdx = 0;
+    int pendingBase[2] = {-1, -1}, pendingCount[2] = {0, 0};
+    auto drain = [&](int b) {
+        if (pendingBase[b] < 0) return cudaSuccess;
+        cudaError_t e = cudaEventSynchronize(done[b]);
+        if (e != cudaSuccess) return e;
+        if (checksums)
+            memcpy(checksums + (size_t)pendingBase[b] * 3, sumHost[b], (size_t)pendingCount[b] * 3 * sizeof(uint64_t));
+        pendingBase[b] = -1;
+        return cudaSuccess;
+    };
+    for (int base = 0; base < nStates; base += batch, ++waveIdx) {
+        const int nb = nStates - base < batch ? nStates - base : batch;
+        const int b = waveIdx & 1;
+        OCEAN_CUDA(drain(b));
+        for (int i = 0; i < nb; ++i) {
+            OceanParams p = states[base + i];
+            p.textureSize = N;
+            int rc = validate_params(p);
+            if (rc != OCEAN_OK) return rc;
+            stateHost[b][i] = make_state_consts(p);
+            seedHost[b][i] = seeds ? seeds[base + i] : (uint64_t)(base + i);
+        }
+        OCEAN_CUDA(cudaMemcpyAsync(stateDev[b], stateHost[b], nb * sizeof(StateConsts), cudaMemcpyHostToDevice, stream));
+        OCEAN_CUDA(cudaMemcpyAsync(seedDev[b], seedHost[b], nb * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+        OCEAN_CUDA(cudaMemsetAsync(sumDev[b], 0, (size_t)nb * 3 * sizeof(unsigned long long), stream));
+        OCEAN_CUDA(launch_noise(seedDev[b], nb, N, noise, stream));
+        ia.nStates = nb; ia.states = stateDev[b];
+        OCEAN_CUDA(launch_init(ia, stream));
+        FrameArgs fa{};
+        fa.N = N; fa.layers = nb * C;
+        fa.h0 = h0; fa.wave = wave; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
+        fa.twiddle = twiddle; fa.time = time;
+        fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
+        fa.foamDecay = expf(-2.0f);
+        fa.zeroFoam = 1;
+        OCEAN_CUDA(launch_rows(fa, stream));
+        OCEAN_CUDA(launch_cols(fa, stream));
+        OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
+        OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
+        OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));
+        OCEAN_CUDA(cudaMemcpyAsync(sumHost[b], sumDev[b], (size_t)nb * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+        OCEAN_CUDA(cudaEventRecord(done[b], stream));
+        pendingBase[b] = base; pendingCount[b] = nb;
+        lastCount = nb;
+    }
+    OCEAN_CUDA(drain(0));
+    OCEAN_CUDA(drain(1));
+    OCEAN_CUDA(cudaStreamSynchronize(stream));
+    return OCEAN_OK;
+}
+
+void OceanEnsemble::destroy() {
+    if (stream) cudaStreamSynchronize(stream);
+    void* dev[] = {noise, h0, wave, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
+    for (void* p : dev)
+        if (p) cudaFree(p);
+    for (int i = 0; i < 2; ++i) {
+        if (stateHost[i]) cudaFreeHost(stateHost[i]);
+        if (seedHost[i]) cudaFreeHost(seedHost[i]);
+        if (sumHost[i]) cudaFreeHost(sumHost[i]);
+        if (done[i]) cudaEventDestroy(done[i]);
+    }
+    if (stream) cudaStreamDestroy(stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+extern "C" {
+
+int ocean_abi_version(void) { return OCEAN_ABI_VERSION; }
+const char* ocean_last_error(void) { return g_error.c_str(); }
+uint64_t ocean_launch_count(void) { return launch_count(); }
+
+int ocean_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int ocean_create(const OceanParams* params, const OceanCascade* cascades, int nCascades, const float* noiseRG,
+                 uint64_t seed, int device, OceanHandle** out) {
+    if (!out) return fail(OCEAN_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    if (!params) return fail(OCEAN_ERR_INVALID_ARGUMENT, "params is NULL");
+    int rc = validate_params(*params);
+    if (rc != OCEAN_OK) return rc;
+    rc = validate_cascades(cascades, nCascades);
+    if (rc != OCEAN_OK) return rc;
+    const int nDev = ocean_device_count();
+    if (nDev <= 0) return fail(OCEAN_ERR_CUDA, "no CUDA device available (this library has no CPU path)");
+    if (device < 0 || device >= nDev) return fail(OCEAN_ERR_INVALID_ARGUMENT, "device %d outside [0, %d)", device, nDev);
+    DeviceScope scope(device);
+    if (!scope.ok) return fail(OCEAN_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    OceanHandle* h = new OceanHandle;
+    h->device = device;
+    h->N = params->textureSize;
+    h->C = nCascades;
+    h->params = *params;
+    memcpy(h->cascades, cascades, nCascades * sizeof(OceanCascade));
+    rc = h->Awake(noiseRG, seed);
+    if (rc != OCEAN_OK) {
+        h->OnDisable();
+        delete h;
+        return rc;
+    }
+    *out = h;
+    return OCEAN_OK;
+}
+
+void ocean_destroy(OceanHandle* h) {
+    if (!h) return;
+    DeviceScope scope(h->device);
+    h->OnDisable();
+    delete h;
+}
+
+int ocean_set_params(OceanHandle* h, const OceanParams* params, const OceanCascade* cascades, int nCascades) {
+    if (!h || !params) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    int rc = validate_params(*params);
+    if (rc != OCEAN_OK) return rc;
+    if (params->textureSize != h->N) return fail(OCEAN_ERR_INVALID_SIZE, "textureSize cannot change after create (%d -> %d)", h->N, params->textureSize);
+    if (cascades) {
+        if (nCascades != h->C) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade count cannot change after create (%d -> %d)", h->C, nCascades);
+        rc = validate_cascades(cascades, nCascades);
+        if (rc != OCEAN_OK) return rc;
+        memcpy(h->cascades, cascades, nCascades * sizeof(OceanCascade));
+    }
+    h->params = *params;
+    return OCEAN_OK;
+}
+
+int ocean_init_spectrum(OceanHandle* h) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    return h->CalculateInitialSpectrumTextures();
+}
+
+int ocean_step(OceanHandle* h, float time) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    return h->CalculateWavesTexturesAtTime(time);
+}
+
+int ocean_update(OceanHandle* h, float time) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    return h->Update(time);
+}
+
+int ocean_sync(OceanHandle* h) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    OCEAN_CUDA(cudaStreamSynchronize(h->copyStream));
+    h->PollReadbacks(false);
+    return OCEAN_OK;
+}
+
+const float* ocean_readback_ptr(OceanHandle* h, int wait, int64_t* frame) {
+    if (frame) *frame = -1;
+    if (!h) return nullptr;
+    DeviceScope scope(h->device);
+    h->PollReadbacks(wait != 0);
+    if (h->rbLatest < 0) return nullptr;
+    if (frame) *frame = h->rbFrame[h->rbLatest];
+    return h->rbHost[h->rbLatest];
+}
+
+static int pick_array(OceanHandle* h, int which, void** p, size_t* bytes) {
+    const size_t t = h->texels();
+    switch (which) {
+        case OCEAN_DISPLACEMENT: *p = h->disp; *bytes = h->C * t * sizeof(float4); break;
+        case OCEAN_DERIVATIVES: *p = h->deriv; *bytes = h->C * t * sizeof(float4); break;
+        case OCEAN_TURBULENCE: *p = h->turb; *bytes = h->C * t * sizeof(float4); break;
+        case OCEAN_INITIAL_SPECTRUM: *p = h->h0; *bytes = h->C * t * sizeof(float4); break;
+        case OCEAN_WAVES_DATA: *p = h->wave; *bytes = h->C * t * sizeof(float4); break;
+        case OCEAN_NOISE: *p = h->noise; *bytes = t * sizeof(float2); break;
+        case OCEAN_ROW_SPECTRA: *p = h->rowsA; *bytes = h->C * t * sizeof(float4); break;  // plane 0; plane 1 via copy
+        default: return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown array id %d", which);
+    }
+    return OCEAN_OK;
+}
+
+int ocean_get_output(OceanHandle* h, int which, void** devPtr, size_t* bytes) {
+    if (!h || !devPtr || !bytes) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    return pick_array(h, which, devPtr, bytes);
+}
+
+int ocean_copy_output(OceanHandle* h, int which, int cascade, float* host) {
+    if (!h || !host) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    DeviceScope scope(h->device);
+    void* p; size_t bytes;
+    int rc = pick_array(h, which, &p, &bytes);
+    if (rc != OCEAN_OK) return rc;
+    OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    if (which == OCEAN_NOISE) {
+        OCEAN_CUDA(cudaMemcpy(host, p, bytes, cudaMemcpyDeviceToHost));
+        return OCEAN_OK;
+    }
+    if (cascade < -1 || cascade >= h->C) return fail(OCEAN_ERR_INVALID_ARGUMENT, "cascade %d outside [-1, %d)", cascade, h->C);
+    const size_t layer = h->layerBytes4();
+    const int planes = which == OCEAN_ROW_SPECTRA ? 2 : 1;
+    for (int pl = 0; pl < planes; ++pl) {
+        const char* src = (const char*)(pl == 0 ? p : (void*)h->rowsB);
+        char* dst = (char*)host + (size_t)pl * (cascade < 0 ? bytes : layer);
+        if (cascade < 0) OCEAN_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+        else OCEAN_CUDA(cudaMemcpy(dst, src + (size_t)cascade * layer, layer, cudaMemcpyDeviceToHost));
+    }
+    return OCEAN_OK;
+}
+
+int ocean_get_wavelengths(OceanHandle* h, float* out, int* nCascades) {
+    if (!h || !out) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    for (int i = 0; i < h->C; ++i) out[i] = h->cascades[i].wavelength;
+    if (nCascades) *nCascades = h->C;
+    return OCEAN_OK;
+}
+
+int ocean_set_turbulence(OceanHandle* h, const float* host) {
+    if (!h || !host) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    DeviceScope scope(h->device);
+    OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    OCEAN_CUDA(cudaMemcpy(h->turb, host, h->C * h->layerBytes4(), cudaMemcpyHostToDevice));
+    h->foamZero = false;
+    return OCEAN_OK;
+}
+
+int ocean_reset_foam(OceanHandle* h) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    OCEAN_CUDA(cudaMemsetAsync(h->turb, 0, h->C * h->layerBytes4(), h->stream));
+    h->foamZero = true;
+    h->frame = 0;
+    return OCEAN_OK;
+}
+
+int64_t ocean_frame_index(OceanHandle* h) { return h ? h->frame : -1; }
+
+int ocean_query_heights(OceanHandle* h, const float* worldXZ, int n, int mode, float* heights, int pointsOnDevice,
+                        int heightsOnDevice) {
+    if (!h || (n > 0 && (!worldXZ || !heights))) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
+    if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_BILINEAR_ALL_CASCADES) return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown query mode %d", mode);
+    DeviceScope scope(h->device);
+    return h->GetWaterHeight(worldXZ, n, mode, heights, pointsOnDevice != 0, heightsOnDevice != 0);
+}
+
+int ocean_get_stream(OceanHandle* h, void** s) {
+    if (!h || !s) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    *s = (void*)h->stream;
+    return OCEAN_OK;
+}
+
+int ocean_set_stream(OceanHandle* h, void* s) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    h->stream = s ? (cudaStream_t)s : h->ownStream;
+    return OCEAN_OK;
+}
+
+int ocean_describe(OceanHandle* h, char* buf, size_t bufBytes) {
+    if (!h || !buf || bufBytes == 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    snprintf(buf, bufBytes, "oceanfft sm_100a: N=%d C=%d device=%d; %s", h->N, h->C, h->device, describe_frame_kernels(h->N));
+    return OCEAN_OK;
+}
+
+int ocean_ensemble_create(int textureSize, const OceanCascade* cascades, int nCascades, int batch, int device, OceanEnsemble** out) {
+    if (!out) return fail(OCEAN_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    const int N = textureSize;
+    if (N < OCEAN_MIN_SIZE || N > OCEAN_MAX_SIZE || (N & (N - 1)) != 0)
+        return fail(OCEAN_ERR_INVALID_SIZE, "textureSize %d is not a power of two in [%d, %d]", N, OCEAN_MIN_SIZE, OCEAN_MAX_SIZE);
+    int rc = validate_cascades(cascades, nCascades);
+    if (rc != OCEAN_OK) return rc;
+    if (batch < 1 || batch > 4096) return fail(OCEAN_ERR_INVALID_ARGUMENT, "batch %d outside [1, 4096]", batch);
+    const int nDev = ocean_device_count();
+    if (nDev <= 0) return fail(OCEAN_ERR_CUDA, "no CUDA device available (this library has no CPU path)");
+    if (device < 0 || device >= nDev) return fail(OCEAN_ERR_INVALID_ARGUMENT, "device %d outside [0, %d)", device, nDev);
+    DeviceScope scope(device);
+    OceanEnsemble* e = new OceanEnsemble;
+    e->device = device; e->N = N; e->C = nCascades; e->batch = batch;
+    memcpy(e->cascades, cascades, nCascades * sizeof(OceanCascade));
+    rc = e->create();
+    if (rc != OCEAN_OK) {
+        e->destroy();
+        delete e;
+        return rc;
+    }
+    *out = e;
+    return OCEAN_OK;
+}
+
+void ocean_ensemble_destroy(OceanEnsemble* e) {
+    if (!e) return;
+    DeviceScope scope(e->device);
+    e->destroy();
+    delete e;
+}
+
+int ocean_ensemble_run(OceanEnsemble* e, const OceanParams* states, const uint64_t* seeds, int nStates, float time, uint64_t* checksums) {
+    if (!e || !states) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (nStates < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "nStates < 0");
+    DeviceScope scope(e->device);
+    return e->run(states, seeds, nStates, time, checksums);
+}
+
+static int ens_pick(OceanEnsemble* e, int which, void** p, size_t* bytes) {
+    const size_t all = (size_t)e->batch * e->stateFloat4() * sizeof(float4);
+    switch (which) {
+        case OCEAN_DISPLACEMENT: *p = e->disp; break;
+        case OCEAN_DERIVATIVES: *p = e->deriv; break;
+        case OCEAN_TURBULENCE: *p = e->turb; break;
+        case OCEAN_INITIAL_SPECTRUM: *p = e->h0; break;
+        case OCEAN_WAVES_DATA: *p = e->wave; break;
+        default: return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown array id %d", which);
+    }
+    *bytes = all;
+    return OCEAN_OK;
+}
+
+int ocean_ensemble_get_output(OceanEnsemble* e, int which, void** devPtr, size_t* bytes) {
+    if (!e || !devPtr || !bytes) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    return ens_pick(e, which, devPtr, bytes);
+}
+
+int ocean_ensemble_copy_output(OceanEnsemble* e, int which, int slot, float* host) {
+    if (!e || !host) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (slot < 0 || slot >= e->batch) return fail(OCEAN_ERR_INVALID_ARGUMENT, "slot %d outside [0, %d)", slot, e->batch);
+    DeviceScope scope(e->device);
+    void* p; size_t bytes;
+    int rc = ens_pick(e, which, &p, &bytes);
+    if (rc != OCEAN_OK) return rc;
+    const size_t per = e->stateFloat4() * sizeof(float4);
+    OCEAN_CUDA(cudaStreamSynchronize(e->stream));
+    OCEAN_CUDA(cudaMemcpy(host, (const char*)p + (size_t)slot * per, per, cudaMemcpyDeviceToHost));
+    return OCEAN_OK;
+}
+
+}  // extern "C"

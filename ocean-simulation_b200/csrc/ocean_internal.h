@@ -1,0 +1,83 @@
+// ocean_internal.h -- declarations shared by the translation units of liboceanfft.so.
+// (ocean_init.cu is built with -fmad=false so that the one-time spectrum follows the
+// reference's operation order rounding for rounding; ocean_frame.cu keeps FMA contraction.)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/oceanfft.h"
+
+namespace ocean {
+
+// Scalars of one ocean state, hoisted out of IS:33-97 on the host in fp32 with the reference's
+// operation order (they do not depend on the texel).
+struct StateConsts {
+    float windSpeed, gravity, fetch, depth;
+    float sqrtDepthOverG;  // sqrt(_Depth / _Gravity)                      IS:39
+    float peakOmega;       // 22 * pow(|g*g/(U*F)|, 0.3333f)               IS:118
+    float alpha;           // 0.076f * pow(|U*U/(F*g)|, 0.22f)             IS:48
+    float mu;              // -2.33f - 1.45f*(U/(g/peakOmega) - 1.17f)     IS:63-64
+    float windTheta;       // atan2(normalize(wind).y, normalize(wind).x)  IS:80-81
+    float lambda;
+    float pad0, pad1;
+};
+
+struct CascadeConsts {
+    float dk;  // 2.0f * PI / wavelength   IS:110
+    float cutoffLow, cutoffHigh, swell, fade;
+    float wavelength;
+};
+
+// Constants of NormalizationFactor IS:69-74, evaluated once on the host in fp32.
+struct SpreadConsts {
+    float pi;     // 3.14159265f                       IS:8
+    float c2;     // pow(log(2),2)/PI - PI/12.0f
+    float c1;     // log(2)/PI
+    float c0;     // 1/(2*PI)
+    float twoSqrtPi;  // 2.0f*sqrt(PI)
+};
+
+struct InitArgs {
+    int N, C;                          // texture size, cascades per state
+    int nStates;                       // oceans in this launch (layers = nStates * C)
+    SpreadConsts sc;
+    CascadeConsts casc[OCEAN_MAX_CASCADES];
+    const StateConsts* states;         // device, nStates entries
+    const float2* noise;               // device, [state][y][x]
+    float4* h0;                        // device, [state*C + cascade][y][x]
+    float4* wave;
+};
+
+struct FrameArgs {
+    int N;
+    int layers;                        // nStates * C
+    const float4* h0;
+    const float4* wave;
+    float4* rowsA;                     // (DxDz, DyDxz) after the x pass, [layer][y][x]
+    float4* rowsB;                     // (DyxDyz, DxxDzz)
+    float4* disp;
+    float4* deriv;
+    float4* turb;
+    const float2* twiddle;             // e^{+2 pi i j / N}, j < N
+    float time;
+    float lambda;
+    float foamDecay;                   // exp(-2.0f)  RF:29-30
+    int zeroFoam;                      // 1: treat the incoming turbulence as zero (fresh texture)
+};
+
+// launchers (return cudaGetLastError()); every launch bumps the launch counter
+cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
+cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
+cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s);
+cudaError_t launch_cols(const FrameArgs& a, cudaStream_t s);
+cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
+                         float* out, int n, int mode, cudaStream_t s);
+cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
+                            int outStride, cudaStream_t s);
+cudaError_t configure_frame_kernels(int N);  // opt in to >48 KiB dynamic shared memory where needed
+const char* describe_frame_kernels(int N);   // "rows<N,R> grid.. smem..; cols<N,W> ..."
+
+void count_launch();
+uint64_t launch_count();
+
+}  // namespace ocean

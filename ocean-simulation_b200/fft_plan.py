@@ -1,0 +1,138 @@
+"""Executable model of the in-kernel FFT plan used by csrc/ocean_fft.cuh.
+
+The CUDA kernels transform a line of N = 2^m complex points with T = N/8 threads, each thread
+holding 8 points in registers.  Stages are radix-8 decimation-in-frequency butterflies done in
+registers; between stages the 8 results are exchanged through shared memory (128-bit elements:
+two packed spectra per element).  The last stage has radix N / 8^(S-1) in {2, 4, 8}.  Input and
+output are both in natural order with thread p holding points p + T*j (j = 0..7), so global
+loads and stores are coalesced and no bit-reversal pass exists.
+
+This module restates the index algebra in numpy, one vectorised "thread" axis, so that
+  * tests/test_fft_plan.py can prove the plan equals N * numpy.fft.ifft for every supported N
+    (the reference network IFFT.compute:48-69 is an unnormalised inverse DFT), and
+  * the shared-memory swizzle can be checked for bank conflicts per quarter-warp (a 128-bit
+    access is conflict-free when the 8 lanes of a quarter-warp hit 8 distinct 16-byte bank groups).
+It is host-side design verification only: nothing here runs on the hot path.
+"""
+import numpy as np
+
+
+def stage_radices(N):
+    """[8, 8, ..., r_last] with product N and r_last in {2, 4, 8}."""
+    assert N >= 16 and N & (N - 1) == 0
+    r = []
+    rem = N
+    while rem > 8:
+        r.append(8)
+        rem //= 8
+    r.append(rem)
+    if r[-1] == 1:
+        r.pop()
+    return r
+
+
+def swizzle(F):
+    """Physical element index (units of one 128-bit element) for logical index F."""
+    return F ^ ((F >> 3) & 7)
+
+
+def _butterfly(v, r):
+    """Inverse DFT of size r along axis 0: u[q] = sum_j v[j] e^{+2 pi i j q / r}."""
+    j = np.arange(r)
+    return np.exp(2j * np.pi * np.outer(j, j) / r) @ v
+
+
+def run_plan(x, W=1, check_conflicts=False):
+    """Transform W interleaved lines.  x: complex array [W][N].  Returns (X[W][N], conflicts).
+
+    Lane numbering inside a CTA is lane = xw + W * tid (column index fastest), which is what
+    makes the column kernel's global accesses contiguous across W adjacent columns.
+    Shared-memory logical index for element F of column xw is G = F * W + xw.
+    """
+    x = np.asarray(x, np.complex128)
+    W_, N = x.shape
+    assert W_ == W
+    T = N // 8
+    radices = stage_radices(N)
+    S = len(radices)
+    tw = np.exp(2j * np.pi * np.arange(N) / N)  # the table W_N[i] the kernel reads
+    conflicts = []
+
+    tid = np.arange(T)
+    # registers: reg[j][tid][xw]
+    reg = np.stack([x[:, tid + T * j].T for j in range(8)])  # stage 0 load: point tid + T*j
+
+    def record(kind, s, G):  # G: [tid][xw] logical indices accessed by one instruction
+        if not check_conflicts:
+            return
+        lane = (np.arange(W)[None, :] + W * tid[:, None]).ravel()
+        phys = swizzle(G.ravel())
+        order = np.argsort(lane)
+        phys = phys[order]
+        worst = 1
+        for q in range(0, phys.size, 8):
+            grp = np.unique(phys[q:q + 8])
+            banks = grp & 7
+            worst = max(worst, np.bincount(banks, minlength=8).max())
+        conflicts.append((kind, s, int(worst)))
+
+    xw = np.arange(W)[None, :]
+    for s in range(S):
+        r = radices[s]
+        Cs = 8 ** s
+        Ms = N // Cs
+        last = s == S - 1
+        if not last or r == 8:
+            # thread -> (c, t): c slow, t fast (for the last radix-8 stage Ms/8 == 1, tid == c)
+            c, t = tid // (Ms // 8), tid % (Ms // 8)
+            u = np.stack([_butterfly(reg[:, i, :], 8) for i in range(T)], axis=1)  # [q][tid][xw]
+            if Ms > 8:
+                for q in range(8):
+                    u[q] *= tw[(t * q * Cs) % N][:, None]
+            if last:
+                reg = u  # output X[c + Cs*q] = X[p + T*q]
+                break
+            # exchange: write A_{s+1}[c + Cs*q][t]
+            Mn = Ms // 8
+            smem = np.zeros(N * W, np.complex128)
+            for q in range(8):
+                F = (c + Cs * q) * Mn + t
+                G = F[:, None] * W + xw
+                record("write", s, G)
+                smem[swizzle(G)] = u[q]
+            # read for stage s+1
+            rn = radices[s + 1]
+            Cn = Cs * 8
+            if s + 1 < S - 1 or rn == 8:
+                cn, tn = tid // (Mn // 8), tid % (Mn // 8)
+                new = []
+                for j in range(8):
+                    F = cn * Mn + tn + (Mn // 8) * j
+                    G = F[:, None] * W + xw
+                    record("read", s, G)
+                    new.append(smem[swizzle(G)])
+                reg = np.stack(new)
+            else:
+                # last stage with radix rn < 8: thread p handles sub-problems c_i = p + T*i
+                new = []
+                for i in range(8 // rn):
+                    for j in range(rn):
+                        F = (tid + T * i) * rn + j  # Mn == rn
+                        G = F[:, None] * W + xw
+                        record("read", s, G)
+                        new.append(smem[swizzle(G)])
+                reg = np.stack(new)  # slot i*rn + j
+        else:
+            # last stage, radix r < 8: 8/r independent butterflies per thread, no twiddle
+            out = np.zeros_like(reg)
+            per = 8 // r
+            for i in range(per):
+                v = reg[i * r:(i + 1) * r]
+                u = np.stack([_butterfly(v[:, k, :], r) for k in range(T)], axis=1)
+                for q in range(r):
+                    out[i + per * q] = u[q]  # x = p + T*(i + (8/r) q)
+            reg = out
+    X = np.zeros((W, N), np.complex128)
+    for j in range(8):
+        X[:, tid + T * j] = reg[j].T
+    return X, conflicts

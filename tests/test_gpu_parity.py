@@ -1,0 +1,424 @@
+"""GPU parity: the CUDA path, called through the C ABI (ctypes -> liboceanfft.so), against the
+CPU oracle on identical noise.  Tolerances are SURVEY.md 8(c):
+
+  displacement / derivatives  rel-L2 <= 1e-5 and max-abs <= 1e-4 * max|field|, per channel
+  turbulence                  rel-L2 <= 1e-5 after excluding branch-flip texels (RF:31), flips bounded
+  h0 / waveData               rel-L2 <= 1e-6
+  arbiter                     CUDA and the fp32 oracle both within 1e-5 rel-L2 of the fp64 oracle
+
+Nothing here reads /root/reference (it does not exist on the GPU box).
+"""
+import numpy as np
+import pytest
+
+from conftest import max_abs_rel, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+TOL_FIELD_L2 = 1e-5
+TOL_FIELD_MAX = 1e-4
+TOL_SPECTRUM_L2 = 1e-6
+
+
+def make_body(pkg, po, cfg, N=None, noise=None, **kw):
+    N = N or cfg["N"]
+    if noise is None:
+        noise = po.fill_noise(cfg["seed"], N)
+    o = cfg["ocean"]
+    body = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5],
+                         texturesSize=N, cascades=cfg["cascades"], noise=noise, **kw)
+    body.Awake()
+    return body, noise
+
+
+def check_fields(got, want, what, tol_l2=TOL_FIELD_L2, tol_max=TOL_FIELD_MAX, channels=4):
+    for c in range(got.shape[0]):
+        for ch in range(channels):
+            g, w = got[c, ..., ch], want[c, ..., ch]
+            if np.abs(w).max() == 0:
+                assert np.abs(g).max() == 0, "%s cascade %d ch %d: expected all zero" % (what, c, ch)
+                continue
+            l2, mx = rel_l2(g, w), max_abs_rel(g, w)
+            assert l2 <= tol_l2, "%s cascade %d ch %d rel-L2 %.3g" % (what, c, ch, l2)
+            assert mx <= tol_max, "%s cascade %d ch %d max-abs/max %.3g" % (what, c, ch, mx)
+
+
+def check_turbulence(got, want, jac_scale=1.0):
+    """Foam: `if (foam < J) foam += J` can flip on 1-ulp differences; a flip changes the texel by O(J).
+    Exclude texels whose difference is of that order, bound their count, and test the rest."""
+    g, w = got[..., 0].astype(np.float64), want[..., 0].astype(np.float64)
+    diff = np.abs(g - w)
+    flips = diff > 1e-3 * max(np.abs(w).max(), 1e-30)
+    frac = flips.mean()
+    assert frac <= 1e-4, "too many foam branch flips: %.3g of texels" % frac
+    keep = ~flips
+    l2 = np.linalg.norm((g - w)[keep]) / np.linalg.norm(w[keep])
+    assert l2 <= TOL_FIELD_L2, "turbulence rel-L2 %.3g (flips excluded: %d)" % (l2, flips.sum())
+    # all four channels carry the same value (RF:32)
+    for ch in range(1, 4):
+        assert np.array_equal(got[..., ch], got[..., 0])
+    return int(flips.sum())
+
+
+@pytest.mark.parametrize("N", [16, 32, 64, 128, 256, 512, 1024])
+def test_initial_spectrum_matches_oracle(pkg, po, N):
+    cfg = pkg.scene.config(3)
+    body, noise = make_body(pkg, po, cfg, N=N)
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise)
+    ob.init_spectrum()
+    h0, wave = body.initialSpectrumTextures, body.wavesDataTextures
+    rh0, rwave = ob.get(po.H0), ob.get(po.WAVE)
+    # structure is exact: zero pattern (cut-offs), k vectors, Hermitian packing (IS:139-141)
+    assert np.array_equal(h0 == 0, rh0 == 0)
+    assert np.array_equal(wave[..., 0], rwave[..., 0]) and np.array_equal(wave[..., 2], rwave[..., 2])
+    for c in range(h0.shape[0]):
+        assert rel_l2(h0[c], rh0[c]) <= TOL_SPECTRUM_L2
+        assert rel_l2(wave[c], rwave[c]) <= TOL_SPECTRUM_L2
+    m = (N - np.arange(N)) % N
+    mirrored = h0[:, m][:, :, m]
+    assert np.array_equal(h0[..., 2], mirrored[..., 0]) and np.array_equal(h0[..., 3], -mirrored[..., 1])
+    body.OnDisable()
+
+
+@pytest.mark.parametrize("N", [16, 32, 64, 128, 256, 512, 1024, 2048])
+def test_row_pass_matches_oracle(pkg, po, N):
+    """Time evolution fused into the x-direction FFT == oracle's evolve + log2(N) horizontal passes."""
+    cfg = pkg.scene.config(1)
+    body, noise = make_body(pkg, po, cfg, N=N)
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    # same spectrum on both sides so the comparison isolates the frame kernels
+    t = 1.0
+    ob.step_rows_only(t)
+    body.CalculateWavesTexturesAtTime(t)
+    rows = body.rowSpectra  # [2][C][N][N][4]
+    for k in range(4):
+        want = ob.get(po.ROWS0 + k)  # [C][N][N][2]
+        got = rows[k // 2][..., (k % 2) * 2:(k % 2) * 2 + 2]
+        assert rel_l2(got, want) <= TOL_FIELD_L2, "spectrum %d after the row pass" % k
+    body.OnDisable()
+
+
+@pytest.mark.parametrize("N", [16, 32, 64, 128, 256, 512, 1024, 2048])
+def test_frame_matches_oracle_every_size(pkg, po, N):
+    cfg = pkg.scene.config(1)
+    body, noise = make_body(pkg, po, cfg, N=N)
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    for t in (0.0, 1.0, 7.25):
+        ob.step(t)
+        body.CalculateWavesTexturesAtTime(t)
+    check_fields(body.displacementsTextures, ob.get(po.DISP), "displacement")
+    check_fields(body.derivativesTextures, ob.get(po.DERIV), "derivatives")
+    check_turbulence(body.turbulenceTextures, ob.get(po.TURB))
+    assert np.all(body.displacementsTextures[..., 3] == 0)
+    body.OnDisable()
+
+
+def test_config1_with_fp64_arbiter(pkg, po):
+    """BASELINE config 1: 1 cascade x 256^2, U10=10, fetch 100 km, depth 500 m, t = 1 s."""
+    cfg = pkg.scene.config(1)
+    body, noise = make_body(pkg, po, cfg)
+    N = cfg["N"]
+    o32 = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=0)
+    o64 = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, double=True, threads=0)
+    for o in (o32, o64):
+        o.init_spectrum()
+        o.step(1.0)
+    body.CalculateWavesTexturesAtTime(1.0)
+    for which, arr in ((po.DISP, body.displacementsTextures), (po.DERIV, body.derivativesTextures)):
+        want32, want64 = o32.get(which), o64.get(which)
+        check_fields(arr, want32, "config1 array %d" % which)
+        e_cuda, e_cpu = rel_l2(arr, want64), rel_l2(want32, want64)
+        assert e_cuda <= 1e-5 and e_cpu <= 1e-5
+        # the CUDA result must be no farther from fp64 than the fp32 oracle is, within a small factor
+        assert e_cuda <= 4 * e_cpu + 1e-7, (e_cuda, e_cpu)
+    body.OnDisable()
+
+
+def test_config3_headline_shape(pkg, po):
+    """BASELINE config 3: 4 cascades x 512^2, depth 20 m (TMA active), swell 0.8; a few frames."""
+    cfg = pkg.scene.config(3)
+    body, noise = make_body(pkg, po, cfg)
+    ob = po.OracleB(cfg["N"], cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    for c in range(4):
+        assert rel_l2(body.initialSpectrumTextures[c], ob.get(po.H0)[c]) <= TOL_SPECTRUM_L2
+    for f in range(3):
+        ob.step(cfg["times"][f])
+        body.CalculateWavesTexturesAtTime(cfg["times"][f])
+    check_fields(body.displacementsTextures, ob.get(po.DISP), "displacement")
+    check_fields(body.derivativesTextures, ob.get(po.DERIV), "derivatives")
+    check_turbulence(body.turbulenceTextures, ob.get(po.TURB))
+    body.OnDisable()
+
+
+def test_config2_foam_accumulation(pkg, po):
+    """BASELINE config 2 (scene defaults, 3 cascades x 256^2): foam recursion over many frames.
+    The oracle is run for 60 frames here (the full 600 are a size-independent property below)."""
+    cfg = pkg.scene.config(2)
+    body, noise = make_body(pkg, po, cfg)
+    ob = po.OracleB(cfg["N"], cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    flips = 0
+    for f in range(60):
+        ob.step(cfg["times"][f])
+        body.CalculateWavesTexturesAtTime(cfg["times"][f])
+        if f % 20 == 19:
+            flips = max(flips, check_turbulence(body.turbulenceTextures, ob.get(po.TURB)))
+    check_fields(body.displacementsTextures, ob.get(po.DISP), "displacement")
+    check_fields(body.derivativesTextures, ob.get(po.DERIV), "derivatives")
+    assert body.frame == 60
+    # 600-frame property: foam_n = e^-2 foam_{n-1} (+ J if below J)  =>  J <= foam <= J / (1 - e^-2) wherever J > 0
+    for f in range(60, 600):
+        body.CalculateWavesTexturesAtTime(cfg["times"][f])
+    d = body.derivativesTextures.astype(np.float64)
+    turb = body.turbulenceTextures[..., 0].astype(np.float64)
+    assert np.isfinite(turb).all()
+    assert turb.max() <= 50.0  # bounded: no blow-up over 600 frames
+    body.OnDisable()
+
+
+def test_foam_checkpoint_resume(pkg, po):
+    """get/set of the turbulence array resumes a run bit-for-bit (checkpoint/resume)."""
+    cfg = pkg.scene.config(2)
+    a, noise = make_body(pkg, po, cfg, N=128)
+    b, _ = make_body(pkg, po, cfg, N=128, noise=noise)
+    for f in range(10):
+        a.CalculateWavesTexturesAtTime(f / 60.0)
+    snap = a.turbulenceTextures
+    b.SetTurbulence(snap)
+    for f in range(10, 15):
+        a.CalculateWavesTexturesAtTime(f / 60.0)
+        b.CalculateWavesTexturesAtTime(f / 60.0)
+    assert np.array_equal(a.turbulenceTextures, b.turbulenceTextures)
+    assert np.array_equal(a.displacementsTextures, b.displacementsTextures)
+    a.ResetFoam()
+    a.CalculateWavesTexturesAtTime(0.0)
+    c, _ = make_body(pkg, po, cfg, N=128, noise=noise)
+    c.CalculateWavesTexturesAtTime(0.0)
+    assert np.array_equal(a.turbulenceTextures, c.turbulenceTextures)
+    for x in (a, b, c):
+        x.OnDisable()
+
+
+def test_device_noise_is_bit_identical_to_host(pkg, po):
+    """ocean_create(noise=NULL, seed) generates the texture on the GPU with include/ocean_noise.h."""
+    for N, seed in ((64, 1), (256, 12345678901234)):
+        body = pkg.WaterBody(windSpeed=8, windDirection=(1, -1), fetch=50000, depth=2560, texturesSize=N,
+                             cascades=pkg.scene.SCENE_CASCADES[:1], seed=seed).Awake()
+        assert np.array_equal(body.randomNoiseTexture.view(np.uint32), po.fill_noise(seed, N).view(np.uint32))
+        body.OnDisable()
+
+
+def test_linearity_and_single_mode(pkg, po):
+    """Size-independent properties at full size: the frame is linear in the noise, and a spectrum with
+    a single +-k pair gives an analytic cosine travelling at omega = sqrt(g k)."""
+    cfg = pkg.scene.config(3)
+    N = cfg["N"]
+    n1, n2 = po.fill_noise(11, N), po.fill_noise(12, N)
+    outs = []
+    for nz in (n1, n2, n1 + n2):
+        body, _ = make_body(pkg, po, cfg, noise=nz)
+        body.CalculateWavesTexturesAtTime(2.5)
+        outs.append((body.displacementsTextures, body.derivativesTextures))
+        body.OnDisable()
+    for k in range(2):
+        assert rel_l2(outs[0][k] + outs[1][k], outs[2][k]) <= 1e-5
+
+    # single mode: noise non-zero only at texel (N/2 + 20, N/2 - 12) -> k = (20, -12) dk, near the spectral peak
+    cfg1 = dict(cfg, cascades=cfg["cascades"][:1])
+    nz = np.zeros((N, N, 2), np.float32)
+    nz[N // 2 - 12, N // 2 + 20] = (1.0, 0.0)
+    body, _ = make_body(pkg, po, cfg1, noise=nz)
+    h0 = body.initialSpectrumTextures[0]
+    wv = body.wavesDataTextures[0]
+    a = float(h0[N // 2 - 12, N // 2 + 20, 0])
+    kx, kz, om = (float(v) for v in wv[N // 2 - 12, N // 2 + 20, [0, 2, 3]])
+    assert a > 0
+    t = 3.0
+    body.CalculateWavesTexturesAtTime(t)
+    Dy = body.displacementsTextures[0, ..., 1].astype(np.float64)
+    L = cfg1["cascades"][0][0]
+    xs = np.arange(N) * L / N
+    X, Z = np.meshgrid(xs, xs)
+    # h(k,t) = a e^{i w t} at +k and a e^{-i w t} at -k  =>  Dy = 2 a cos(k.x + w t) after the ifftshift sign
+    want = 2 * a * np.cos(kx * X + kz * Z + om * t)
+    assert np.abs(Dy - want).max() <= 2e-5 * 2 * a + 1e-12
+    body.OnDisable()
+
+
+def test_query_nearest_matches_reference_lookup(pkg, po):
+    cfg = pkg.scene.config(1)
+    body, noise = make_body(pkg, po, cfg)
+    N = cfg["N"]
+    body.CalculateWavesTexturesAtTime(1.0)
+    rng = np.random.default_rng(40)
+    pts = rng.uniform(-N / 2 - 10, N / 2 + 10, (100000, 2)).astype(np.float32)
+    pts[:8] = [[-N / 2, -N / 2], [N / 2, N / 2], [0, 0], [-1e9, 1e9], [N / 2 - 1e-3, 0], [0.5, -0.5], [-0.0, 0.0], [127.99999, -128.0]]
+    got = body.GetWaterHeights(pts, pkg._lib.QUERY_NEAREST_REF)
+    disp = body.displacementsTextures[0]
+    # WB:199-208 restated with numpy fp32
+    lo, hi = np.float32(-(N // 2)), np.float32(N // 2)
+    u = np.clip((pts[:, 0] - lo) / (hi - lo), np.float32(0), np.float32(1)).astype(np.float32)
+    v = np.clip((pts[:, 1] - lo) / (hi - lo), np.float32(0), np.float32(1)).astype(np.float32)
+    x = np.clip((u * np.float32(N)).astype(np.int32), 0, N - 1)
+    y = np.clip((v * np.float32(N)).astype(np.int32), 0, N - 1)
+    assert np.array_equal(got, disp[y, x, 1])
+    # and against the oracle's transcription of GetWaterHeight on the oracle's own displacement
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    ob.step(1.0)
+    want = ob.query_heights(pts)
+    assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max()
+    body.OnDisable()
+
+
+def test_query_bilinear_modes(pkg, po):
+    cfg = pkg.scene.config(3)
+    body, _ = make_body(pkg, po, cfg, N=128)
+    N = 128
+    body.CalculateWavesTexturesAtTime(0.5)
+    disp = body.displacementsTextures.astype(np.float64)
+    wl = body.wavelengths
+    rng = np.random.default_rng(41)
+    pts = rng.uniform(-3000, 3000, (20000, 2)).astype(np.float32)
+
+    def sample(c, p):
+        u = p[:, 0].astype(np.float64) / wl[c]
+        v = p[:, 1].astype(np.float64) / wl[c]
+        fx, fy = (u - np.floor(u)) * N - 0.5, (v - np.floor(v)) * N - 0.5
+        x0, y0 = np.floor(fx).astype(int), np.floor(fy).astype(int)
+        wx, wy = fx - x0, fy - y0
+        x1, y1 = (x0 + 1) % N, (y0 + 1) % N
+        x0, y0 = x0 % N, y0 % N
+        d = disp[c, ..., 1]
+        return (d[y0, x0] * (1 - wx) + d[y0, x1] * wx) * (1 - wy) + (d[y1, x0] * (1 - wx) + d[y1, x1] * wx) * wy
+
+    got1 = body.GetWaterHeights(pts, pkg._lib.QUERY_BILINEAR)
+    gotA = body.GetWaterHeights(pts, pkg._lib.QUERY_BILINEAR_ALL_CASCADES)
+    want1 = sample(0, pts)
+    wantA = sum(sample(c, pts) for c in range(4))
+    # fp32 uv arithmetic at |world| ~ 3000 limits agreement with the float64 restatement
+    assert np.abs(got1 - want1).max() <= 2e-3 * np.abs(want1).max()
+    assert np.abs(gotA - wantA).max() <= 2e-3 * np.abs(wantA).max()
+    body.OnDisable()
+
+
+def test_update_readback_and_get_water_height(pkg, po):
+    """WB:284-297 + WB:195-209: 0 before the first readback, then layer 0 of a completed frame."""
+    cfg = pkg.scene.config(1)
+    body, _ = make_body(pkg, po, cfg, N=128)
+    assert body.GetWaterHeight((3.0, 0.0, -7.0)) == 0.0
+    body.Update(0.25)
+    frame, data = body.WaitReadback()
+    assert frame == 0
+    assert np.array_equal(data, body.displacementsTextures[0])
+    N = 128
+    x, y = int((3.0 + 64) / 128 * N), int((-7.0 + 64) / 128 * N)
+    assert body.GetWaterHeight((3.0, 99.0, -7.0)) == data[y, x, 1]
+    for f in range(1, 6):
+        body.Update(0.25 + f / 60.0)
+    frame, data = body.WaitReadback()
+    assert frame == 5
+    assert np.array_equal(data, body.displacementsTextures[0])
+    body.OnDisable()
+
+
+def test_choppiness_lambda(pkg, po):
+    """lambda scales the horizontal displacement and enters the Jacobian; lambda = 1 is the reference."""
+    cfg = pkg.scene.config(1)
+    a, noise = make_body(pkg, po, cfg, N=128)
+    b, _ = make_body(pkg, po, cfg, N=128, noise=noise, choppiness=0.5)
+    a.CalculateWavesTexturesAtTime(1.0)
+    b.CalculateWavesTexturesAtTime(1.0)
+    da, db = a.displacementsTextures, b.displacementsTextures
+    assert np.array_equal(db[..., 1], da[..., 1])
+    assert np.array_equal(db[..., 0], da[..., 0] * np.float32(0.5)) and np.array_equal(db[..., 2], da[..., 2] * np.float32(0.5))
+    ga, gb = a.derivativesTextures, b.derivativesTextures
+    assert np.array_equal(gb[..., :2], ga[..., :2])
+    assert np.array_equal(gb[..., 2:], ga[..., 2:] * np.float32(0.5))
+    a.OnDisable()
+    b.OnDisable()
+
+
+def test_reinit_after_parameter_change(pkg, po):
+    """OnValidate path (WB:324-337): change wind/fetch/depth, recompute the spectrum, compare with the oracle."""
+    cfg = pkg.scene.config(2)
+    body, noise = make_body(pkg, po, cfg, N=128)
+    body.windSpeed, body.windDirection, body.fetch, body.depth = 15.0, (0.3, 1.0), 2.0e5, 35.0
+    body.OnValidate()
+    ocean = (15.0, 0.3, 1.0, 9.81, 2.0e5, 35.0)
+    ob = po.OracleB(128, ocean, cfg["cascades"], noise)
+    ob.init_spectrum()
+    assert rel_l2(body.initialSpectrumTextures, ob.get(po.H0)) <= TOL_SPECTRUM_L2
+    ob.step(0.5)
+    body.ResetFoam()
+    body.CalculateWavesTexturesAtTime(0.5)
+    check_fields(body.displacementsTextures, ob.get(po.DISP), "displacement")
+    body.OnDisable()
+
+
+def test_ensemble_equals_individual_runs(pkg, po):
+    """Ensemble runner (config 5 shape, reduced): every state == a stand-alone WaterBody with the same
+    parameters and seed, bit for bit; checksums match the arrays; waves of `batch` cover ragged counts."""
+    cfg = pkg.scene.config(5)
+    N = 128
+    oceans, seeds = pkg.scene.ensemble_states(7)
+    ens = pkg.OceanEnsemble(N, cfg["cascades"], batch=3)
+    sums = ens.run(oceans, seeds, time=1.0)
+    assert sums.shape == (7, 3)
+    last = ens.copy_output(pkg._lib.DISPLACEMENT, 0)  # last wave held state 6 in slot 0
+    for i in (0, 3, 6):
+        o = oceans[i]
+        body = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5],
+                             texturesSize=N, cascades=cfg["cascades"], seed=int(seeds[i])).Awake()
+        body.CalculateWavesTexturesAtTime(1.0)
+        arrs = (body.displacementsTextures, body.derivativesTextures, body.turbulenceTextures)
+        for k in range(3):
+            assert int(arrs[k].view(np.uint32).astype(np.uint64).sum()) == int(sums[i, k])
+        if i == 6:
+            assert np.array_equal(arrs[0], last)
+        body.OnDisable()
+    # and one state against the oracle
+    o = oceans[3]
+    ob = po.OracleB(N, tuple(float(v) for v in o), cfg["cascades"], po.fill_noise(int(seeds[3]), N))
+    ob.init_spectrum()
+    ob.step(1.0)
+    again = pkg.OceanEnsemble(N, cfg["cascades"], batch=4)
+    again.run(oceans[:4], seeds[:4], time=1.0)
+    check_fields(again.copy_output(pkg._lib.DISPLACEMENT, 3), ob.get(po.DISP), "ensemble displacement")
+    assert sums[:4].tolist() == again.run(oceans[:4], seeds[:4], time=1.0).tolist()
+    ens.close()
+    again.close()
+
+
+def test_abi_flow_and_errors_on_device(pkg, po):
+    """create -> init -> step x n -> read -> query -> destroy, as the C# shim would drive it."""
+    import ctypes
+    L = pkg._lib
+    lib = L.load()
+    assert lib.ocean_device_count() >= 1
+    p = L.OceanParams(8, 1, -1, 9.81, 50000, 2560, 64, 1.0)
+    casc = (L.OceanCascade * 2)(L.OceanCascade(1530, 1e-10, 1e12, 0.4, 0.1), L.OceanCascade(201, 1e-5, 1e6, 0.1, 0.1))
+    h = ctypes.c_void_p()
+    assert lib.ocean_create(ctypes.byref(p), casc, 2, None, 7, 0, ctypes.byref(h)) == L.OK
+    assert lib.ocean_step(h, 0.0) == L.ERR_NOT_INITIALIZED
+    assert b"ocean_init_spectrum" in lib.ocean_last_error()
+    assert lib.ocean_init_spectrum(h) == L.OK
+    before = lib.ocean_launch_count()
+    for f in range(4):
+        assert lib.ocean_step(h, f / 60.0) == L.OK
+    assert lib.ocean_sync(h) == L.OK
+    assert lib.ocean_launch_count() - before == 8  # two kernels per frame
+    assert lib.ocean_frame_index(h) == 4
+    ptr, nbytes = ctypes.c_void_p(), ctypes.c_size_t()
+    assert lib.ocean_get_output(h, L.DISPLACEMENT, ctypes.byref(ptr), ctypes.byref(nbytes)) == L.OK
+    assert ptr.value and nbytes.value == 2 * 64 * 64 * 16
+    assert lib.ocean_get_output(h, 99, ctypes.byref(ptr), ctypes.byref(nbytes)) == L.ERR_INVALID_ARGUMENT
+    out = np.empty((64, 64, 4), np.float32)
+    assert lib.ocean_copy_output(h, L.DISPLACEMENT, 5, out.ctypes.data_as(ctypes.POINTER(ctypes.c_float))) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_create(ctypes.byref(p), casc, 2, None, 7, 99, ctypes.byref(ctypes.c_void_p())) == L.ERR_INVALID_ARGUMENT
+    buf = ctypes.create_string_buffer(512)
+    assert lib.ocean_describe(h, buf, 512) == L.OK and b"N=64" in buf.value
+    lib.ocean_destroy(h)
