@@ -123,6 +123,10 @@ int ocean_init_spectrum(OceanHandle* h);
  * advances the foam recursion by exactly one frame.  Asynchronous. */
 int ocean_step(OceanHandle* h, float time);
 int ocean_sync(OceanHandle* h); /* block until everything enqueued on the handle has finished */
+/* Measurement hook: enqueue only one half of a frame so each kernel can be bracketed by events.
+ * which = 1: row pass (TD:20-47 + FFT:48-57), which = 2: column pass + assembly (FFT:60-78 + RF:16-34,
+ * advances foam and the frame index), which = 0: both (== ocean_step). */
+int ocean_step_partial(OceanHandle* h, float time, int which);
 
 /* WaterBody.Update WB:284-297: ocean_step(time) + AsyncGPUReadback.Request of displacement
  * layer 0 (WB:288) into library-owned pinned memory on a second stream.  The readback becomes

@@ -4,7 +4,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liboceanfft.so")
+LIB_PATH = os.environ.get("OCEANFFT_LIB") or os.path.join(HERE, "liboceanfft.so")  # env override: tuning variants
 
 OCEAN_MAX_CASCADES = 5
 
@@ -18,7 +18,7 @@ QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCAD
 # every symbol include/oceanfft.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = [
     "ocean_abi_version", "ocean_last_error", "ocean_device_count", "ocean_create", "ocean_destroy",
-    "ocean_set_params", "ocean_init_spectrum", "ocean_step", "ocean_sync", "ocean_update",
+    "ocean_set_params", "ocean_init_spectrum", "ocean_step", "ocean_step_partial", "ocean_sync", "ocean_update",
     "ocean_readback_ptr", "ocean_get_output", "ocean_copy_output", "ocean_get_wavelengths",
     "ocean_set_turbulence", "ocean_reset_foam", "ocean_frame_index", "ocean_query_heights",
     "ocean_get_stream", "ocean_set_stream", "ocean_launch_count", "ocean_describe",
@@ -68,6 +68,7 @@ def load():
     L.ocean_set_params.argtypes = [vp, ctypes.POINTER(OceanParams), ctypes.POINTER(OceanCascade), ctypes.c_int]
     L.ocean_init_spectrum.argtypes = [vp]
     L.ocean_step.argtypes = [vp, ctypes.c_float]
+    L.ocean_step_partial.argtypes = [vp, ctypes.c_float, ctypes.c_int]
     L.ocean_sync.argtypes = [vp]
     L.ocean_update.argtypes = [vp, ctypes.c_float]
     L.ocean_readback_ptr.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_int64)]

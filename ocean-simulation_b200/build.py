@@ -38,8 +38,14 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def build(force=False, verbose=False):
-    """Compile every CUDA translation unit for sm_100a and link liboceanfft.so.  Returns the path."""
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile every CUDA translation unit for sm_100a and link liboceanfft.so.  Returns the path.
+    `defines` / `out` build a tuning variant (e.g. ["-DOCEAN_COLS512_W=4"]) into another file."""
+    global OBJ, LIB
+    if out:
+        OBJ = os.path.join(CSRC, "build_" + os.path.basename(out).replace(".so", ""))
+        LIB = out
+        force = True
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()
     hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
@@ -51,7 +57,7 @@ def build(force=False, verbose=False):
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
             # use the PATH gcc: the image's CXX=/opt/gcc/bin/g++ wrapper is not a full toolchain
-            cmd = [nvcc, "-ccbin", "g++"] + ARCH + COMMON + extra + ["-c", s, "-o", o]
+            cmd = [nvcc, "-ccbin", "g++"] + ARCH + COMMON + extra + list(defines) + ["-c", s, "-o", o]
             r = subprocess.run(cmd, capture_output=True, text=True)
             log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
             if r.returncode != 0:

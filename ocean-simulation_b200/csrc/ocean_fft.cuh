@@ -77,8 +77,12 @@ constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
 // N points per line, NL lines per CTA.  INTERLEAVED = lines are adjacent columns (column kernel:
 // CTA lane = line + NL*tid) and share one interleaved buffer, else every line owns a region
 // (row kernel: CTA lane = tid + T*line).  DOUBLE_BUF trades shared memory for one barrier per
-// exchange instead of two.
-template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF>
+// exchange instead of two.  DENSE0: exchange 0 is unswizzled (a TMA tensor copy staged the line in
+// natural order in the same buffer); otherwise every exchange is XOR-swizzled.
+//
+// Twiddles: table tw[(s*7 + q-1)*T + tid] = e^{+2 pi i t q C_s / N}, t = tid mod (M_s/8), one entry
+// per (stage, q, thread) so that a warp reads 32 consecutive float2 (see make_twiddles, ocean_host.cu).
+template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF, bool DENSE0 = false>
 struct LineFFT {
     static constexpr int T = N / 8;
     static constexpr int LOGN = ilog2(N);
@@ -91,10 +95,13 @@ struct LineFFT {
 
     // logical element F of line `ln` -> physical float4 index; XOR swizzle keeps every 128-bit
     // access of a quarter-warp on 8 distinct 16-byte bank groups (checked in fft_plan.py)
+    template <int s>
     __device__ static __forceinline__ int phys(int F, int ln) {
         int G = INTERLEAVED ? (F * NL + ln) : (ln * N + F);
+        if constexpr (DENSE0 && s == 0) return G;
         return G ^ ((G >> 3) & 7);
     }
+    static constexpr int TWIDDLE_ENTRIES = (S - 1) * 7 * T;
 
     template <int s>
     __device__ static __forceinline__ void stage(float4 (&reg)[8], float4* __restrict__ smem, const int tid,
@@ -105,10 +112,9 @@ struct LineFFT {
         if constexpr (!last || RLAST == 8) {
             radix8_inv(reg);
             if constexpr (Ms > 8) {
-                const int t = tid & (Ms / 8 - 1);
 #pragma unroll
                 for (int q = 1; q < 8; ++q) {
-                    const float2 w = __ldg(&tw[t * q * Cs]);
+                    const float2 w = __ldg(&tw[(s * 7 + q - 1) * T + tid]);
                     const float4 r = reg[q];
                     reg[q] = make_float4(r.x * w.x - r.y * w.y, r.x * w.y + r.y * w.x,
                                          r.z * w.x - r.w * w.y, r.z * w.y + r.w * w.x);
@@ -121,19 +127,19 @@ struct LineFFT {
                     if (prior + s > 0) __syncthreads();  // previous exchange fully read
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q) buf[phys(tid + T * q, ln)] = reg[q];
+                for (int q = 0; q < 8; ++q) buf[phys<s>(tid + T * q, ln)] = reg[q];
                 __syncthreads();
                 constexpr int rn = (s + 1 == S - 1) ? RLAST : 8;
                 if constexpr (rn == 8) {
                     constexpr int Q = Mn / 8;  // threads per sub-problem in the next stage
                     const int cn = tid / Q, tn = tid & (Q - 1);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) reg[j] = buf[phys((cn * 8 + j) * Q + tn, ln)];
+                    for (int j = 0; j < 8; ++j) reg[j] = buf[phys<s>((cn * 8 + j) * Q + tn, ln)];
                 } else {
 #pragma unroll
                     for (int i = 0; i < 8 / rn; ++i)
 #pragma unroll
-                        for (int j = 0; j < rn; ++j) reg[i * rn + j] = buf[phys((tid + T * i) * rn + j, ln)];
+                        for (int j = 0; j < rn; ++j) reg[i * rn + j] = buf[phys<s>((tid + T * i) * rn + j, ln)];
                 }
             }
         } else if constexpr (RLAST == 4) {

@@ -8,7 +8,7 @@
 //                        fused with Permute (FFT:73-78) and FillResultTextures (RF:16-34):
 //                        (-1)^(x+y), unpack, lambda, Jacobian, foam recursion, 128-bit stores.
 //
-// Bytes per texel-cascade: rows read h0 16 + waveData 16 and write 32 of intermediate; cols
+// Bytes per texel-cascade: rows read h0 16 + (1/|k|, omega) 8 and write 32 of intermediate; cols
 // read that 32 (L2-resident) + turbulence 16 and write 3 x 16.  Algorithmic = 96 B.
 // Bandwidth-bound fp32 FFT: tensor cores are not used (no dense contraction here).
 #include <stdio.h>
@@ -22,21 +22,58 @@ namespace ocean {
 __device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
 
+// Ampere-style asynchronous copies (LDGSTS): global -> shared without a register round trip, so a
+// thread can have its whole row in flight while holding no data registers.
+// (The .L2::cache_hint form of the 16-byte copy raised "illegal instruction" on sm_100a / driver 580
+// for some launch shapes, so the copies carry no explicit L2 policy.)
+__device__ __forceinline__ void cp_async16(void* smemDst, const void* g) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smemDst, const void* g) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// tuning knobs for the headline size (overridable at build time for experiments)
+#ifndef OCEAN_ROWS512_R
+#define OCEAN_ROWS512_R 1
+#endif
+#ifndef OCEAN_ROWS512_MINB
+#define OCEAN_ROWS512_MINB 14
+#endif
+#ifndef OCEAN_ROWS512_DB
+#define OCEAN_ROWS512_DB false
+#endif
+#ifndef OCEAN_COLS512_W
+#define OCEAN_COLS512_W 8
+#endif
+#ifndef OCEAN_COLS512_MINB
+#define OCEAN_COLS512_MINB 2
+#endif
+#ifndef OCEAN_COLS512_DB
+#define OCEAN_COLS512_DB false
+#endif
+
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
-    static constexpr int R = (T >= 64) ? 1 : 64 / T;  // rows per CTA: CTA >= 64 threads
+    static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
     static constexpr int THREADS = R * T;
-    static constexpr bool DB = (N != 512);            // N=512: single buffer so 14 CTAs fit per SM
-    static constexpr int MINB = (N == 512) ? 14 : 1;
-    using FFT = LineFFT<N, R, false, DB>;
+    static constexpr int MINB = (N == 512) ? OCEAN_ROWS512_MINB : 1;
+    // the staged h0 row doubles as the (single) exchange buffer; every exchange is swizzled
+    using FFT = LineFFT<N, R, false, false, false>;
+    static constexpr int SMEM_BYTES = R * N * (16 + 8);  // h0 float4 + (1/|k|, omega) float2 per texel
 };
 
 template <int N> struct ColCfg {
     static constexpr int T = N / 8;
-    static constexpr int W = (T >= 64) ? 2 : ((T >= 32) ? 4 : 8);  // adjacent columns per CTA
+    static constexpr int W = (N == 512) ? OCEAN_COLS512_W : ((T >= 64) ? 2 : ((T >= 32) ? 4 : 8));  // adjacent columns per CTA
     static constexpr int THREADS = W * T;
-    static constexpr bool DB = (N != 512);
-    static constexpr int MINB = (N == 512) ? 7 : 1;
+    static constexpr bool DB = (N == 512) ? OCEAN_COLS512_DB : true;
+    static constexpr int MINB = (N == 512) ? OCEAN_COLS512_MINB : 1;
     using FFT = LineFFT<N, W, true, DB>;
 };
 
@@ -45,30 +82,48 @@ template <int N>
 __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_rows_kernel(const FrameArgs a) {
     using Cfg = RowCfg<N>;
     using FFT = typename Cfg::FFT;
-    constexpr int T = Cfg::T;
+    constexpr int T = Cfg::T, R = Cfg::R;
     extern __shared__ float4 smem[];
+    float4* hs = smem;                             // [R][N] staged h0, then the exchange buffer
+    float2* ws = (float2*)(smem + R * N);          // [R][N] staged (1/|k|, omega)
     const int tid = threadIdx.x & (T - 1);
     const int row = threadIdx.x / T;
     const size_t totalRows = (size_t)a.layers * N;
-    size_t line = (size_t)blockIdx.x * Cfg::R + row;  // = layer*N + y
+    size_t line = (size_t)blockIdx.x * R + row;  // = layer*N + y
     const bool active = line < totalRows;
     if (!active) line = totalRows - 1;  // keep every thread in the barriers; results are dropped
     const float4* __restrict__ H = a.h0 + line * N;
-    const float4* __restrict__ Wd = a.wave + line * N;
+    const float2* __restrict__ Wd = a.waveHot + line * N;
+
+    // Stage the whole row: 16 asynchronous copies per thread are in flight before any arithmetic.
+    // Element x lands in the slot exchange 0 will later use for it, and thread `tid` only ever
+    // touches its own 8 elements (x = tid + T*j), so no barrier is needed around the staging.
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int x = tid + T * j;
+        cp_async16(&hs[FFT::template phys<0>(x, row)], H + x);
+        cp_async8(&ws[row * N + x], Wd + x);
+    }
+    const int layer = (int)(line / N), y = (int)(line & (N - 1));
+    const float dk = a.dk[layer % a.C];
+    const float kz = (float)(y - N / 2) * dk;  // IS:111 (waveData.z)
     const float time = a.time;
+    cp_async_wait_all();
 
     float4 pa[8], pb[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float4 h0 = ld_stream(H + tid + T * j);
-        const float4 wv = ld_stream(Wd + tid + T * j);
+        const int x = tid + T * j;
+        const float4 h0 = hs[FFT::template phys<0>(x, row)];
+        const float2 wv = ws[row * N + x];
+        const float kx = (float)(x - N / 2) * dk;  // IS:111 (waveData.x)
+        const float ik = wv.x;
         // TD:23-26
         float sn, cs;
-        sincosf(wv.w * time, &sn, &cs);
+        sincosf(wv.y * time, &sn, &cs);
         const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
         const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
         const float ihx = -hy, ihy = hx;
-        const float kx = wv.x, ik = wv.y, kz = wv.z;
         // TD:29-40
         const float ydx_x = ihx * kx, ydx_y = ihy * kx;
         const float ydz_x = ihx * kz, ydz_y = ihy * kz;
@@ -231,7 +286,7 @@ template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t
     using Cfg = RowCfg<N>;
     const size_t totalRows = (size_t)a.layers * N;
     const unsigned grid = (unsigned)((totalRows + Cfg::R - 1) / Cfg::R);
-    ocean_rows_kernel<N><<<grid, Cfg::THREADS, Cfg::FFT::SMEM_BYTES, s>>>(a);
+    ocean_rows_kernel<N><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(a);
     count_launch();
     return cudaGetLastError();
 }
@@ -243,7 +298,7 @@ template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t
     return cudaGetLastError();
 }
 template <int N> static cudaError_t configure() {
-    cudaError_t e = cudaFuncSetAttribute(ocean_rows_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, RowCfg<N>::FFT::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(ocean_rows_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, RowCfg<N>::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(ocean_cols_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColCfg<N>::FFT::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -256,7 +311,7 @@ template <int N> static const char* describe() {
     static char buf[256];
     snprintf(buf, sizeof buf,
              "rows<N=%d>: %d rows/CTA, %d threads, %d B smem, %s buffer; cols<N=%d>: %d columns/CTA, %d threads, %d B smem, %s buffer",
-             N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::FFT::SMEM_BYTES, RowCfg<N>::DB ? "double" : "single", N,
+             N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::SMEM_BYTES, "single", N,
              ColCfg<N>::W, ColCfg<N>::THREADS, ColCfg<N>::FFT::SMEM_BYTES, ColCfg<N>::DB ? "double" : "single");
     return buf;
 }

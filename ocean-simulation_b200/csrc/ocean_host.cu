@@ -121,15 +121,25 @@ static CascadeConsts make_cascade_consts(const OceanCascade& c) {
     return k;
 }
 
-// e^{+2 pi i j / N}: the table the radix-8 stages index (replaces the butterfly texture of
-// IFFT.cs:36 / FFT:37-45).  Evaluated in double, rounded once.
+// Twiddle table of the radix-8 stages (replaces the butterfly texture of IFFT.cs:36 / FFT:37-45):
+// tw[(s*7 + q-1)*T + tid] = e^{+2 pi i * t*q*8^s / N} with T = N/8, t = tid mod (N / 8^(s+1)),
+// for the S-1 twiddled stages.  One entry per (stage, q, thread): warps read consecutive float2.
+// Evaluated in double, rounded once.
 static std::vector<float2> make_twiddles(int N) {
-    std::vector<float2> t(N);
-    for (int j = 0; j < N; ++j) {
-        const double a = 2.0 * M_PI * (double)j / (double)N;
-        t[j] = make_float2((float)cos(a), (float)sin(a));
+    int logN = 0;
+    while ((1 << logN) < N) ++logN;
+    const int S = (logN + 2) / 3, T = N / 8;
+    std::vector<float2> tw((size_t)(S > 1 ? S - 1 : 1) * 7 * T, make_float2(1.0f, 0.0f));
+    for (int s = 0; s + 1 < S; ++s) {
+        const int Cs = 1 << (3 * s), Ms = N / Cs;
+        for (int q = 1; q < 8; ++q)
+            for (int tid = 0; tid < T; ++tid) {
+                const int t = tid & (Ms / 8 - 1);
+                const double a = 2.0 * M_PI * (double)((long long)t * q * Cs % N) / (double)N;
+                tw[(size_t)(s * 7 + q - 1) * T + tid] = make_float2((float)cos(a), (float)sin(a));
+            }
     }
-    return t;
+    return tw;
 }
 
 }  // namespace ocean
@@ -148,6 +158,7 @@ struct OceanHandle {
     float2* noise = nullptr;
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr;
     float4 *disp = nullptr, *deriv = nullptr, *turb = nullptr;
+    float2* waveHot = nullptr;  // (1/|k|, omega): compact copy of waveData read by the frame kernels
     float2* twiddle = nullptr;
     StateConsts* stateDev = nullptr;
     uint64_t* seedDev = nullptr;
@@ -174,7 +185,7 @@ struct OceanHandle {
 
     int Awake(const float* noiseHost, uint64_t seed);
     int CalculateInitialSpectrumTextures();
-    int CalculateWavesTexturesAtTime(float time);
+    int CalculateWavesTexturesAtTime(float time, int which = 0);
     int Update(float time);
     void PollReadbacks(bool wait);
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
@@ -189,19 +200,20 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&noise, t * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&h0, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&wave, C * t * sizeof(float4)));
+    OCEAN_CUDA(cudaMalloc(&waveHot, C * t * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&rowsA, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&rowsB, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&disp, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&deriv, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&turb, C * t * sizeof(float4)));
-    OCEAN_CUDA(cudaMalloc(&twiddle, N * sizeof(float2)));
+    const std::vector<float2> tw = make_twiddles(N);
+    OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&stateDev, sizeof(StateConsts)));
     OCEAN_CUDA(cudaMalloc(&seedDev, sizeof(uint64_t)));
     OCEAN_CUDA(cudaMemsetAsync(disp, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(deriv, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(turb, 0, C * t * sizeof(float4), stream));  // fresh RenderTexture
-    const std::vector<float2> tw = make_twiddles(N);
-    OCEAN_CUDA(cudaMemcpyAsync(twiddle, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice, stream));
+    OCEAN_CUDA(cudaMemcpyAsync(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, stream));
     if (noiseHost) {  // GenerateRandomNoiseTexture WB:86-100: the caller supplies the texture
         OCEAN_CUDA(cudaMemcpyAsync(noise, noiseHost, t * sizeof(float2), cudaMemcpyHostToDevice, stream));
     } else {          // ... or it is generated on the device from the seed
@@ -226,26 +238,29 @@ int OceanHandle::CalculateInitialSpectrumTextures() {
     a.N = N; a.C = C; a.nStates = 1;
     a.sc = make_spread_consts();
     for (int i = 0; i < C; ++i) a.casc[i] = make_cascade_consts(cascades[i]);
-    a.states = stateDev; a.noise = noise; a.h0 = h0; a.wave = wave;
+    a.states = stateDev; a.noise = noise; a.h0 = h0; a.wave = wave; a.waveHot = waveHot;
     OCEAN_CUDA(launch_init(a, stream));
     OCEAN_CUDA(cudaStreamSynchronize(stream));  // `sc` is stack memory
     spectrumReady = true;
     return OCEAN_OK;
 }
 
-int OceanHandle::CalculateWavesTexturesAtTime(float time) {
+int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_step before ocean_init_spectrum");
     FrameArgs a{};
-    a.N = N; a.layers = C;
-    a.h0 = h0; a.wave = wave; a.rowsA = rowsA; a.rowsB = rowsB;
+    a.N = N; a.layers = C; a.C = C;
+    for (int i = 0; i < C; ++i) a.dk[i] = make_cascade_consts(cascades[i]).dk;
+    a.h0 = h0; a.waveHot = waveHot; a.rowsA = rowsA; a.rowsB = rowsB;
     a.disp = disp; a.deriv = deriv; a.turb = turb; a.twiddle = twiddle;
     a.time = time; a.lambda = params.lambda;
     a.foamDecay = expf(-2.0f);  // RF:29-30
     a.zeroFoam = foamZero ? 1 : 0;
-    OCEAN_CUDA(launch_rows(a, stream));
-    OCEAN_CUDA(launch_cols(a, stream));
-    foamZero = false;
-    ++frame;
+    if (which == 0 || which == 1) OCEAN_CUDA(launch_rows(a, stream));
+    if (which == 0 || which == 2) {
+        OCEAN_CUDA(launch_cols(a, stream));
+        foamZero = false;
+        ++frame;
+    }
     return OCEAN_OK;
 }
 
@@ -338,7 +353,7 @@ int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* he
 void OceanHandle::OnDisable() {
     if (stream) cudaStreamSynchronize(stream);
     if (copyStream) cudaStreamSynchronize(copyStream);
-    void* dev[] = {noise, h0, wave, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
+    void* dev[] = {noise, h0, wave, waveHot, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -358,6 +373,7 @@ struct OceanEnsemble {
     cudaStream_t stream = nullptr;
     float2* noise = nullptr;
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
+    float2* waveHot = nullptr;
     float2* twiddle = nullptr;
     // double-buffered parameter / result staging so consecutive waves overlap
     StateConsts* stateDev[2] = {nullptr, nullptr};
@@ -381,9 +397,10 @@ int OceanEnsemble::create() {
     OCEAN_CUDA(cudaMalloc(&noise, batch * t * sizeof(float2)));
     float4** arrs[] = {&h0, &wave, &rowsA, &rowsB, &disp, &deriv, &turb};
     for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
-    OCEAN_CUDA(cudaMalloc(&twiddle, N * sizeof(float2)));
+    OCEAN_CUDA(cudaMalloc(&waveHot, (size_t)batch * C * t * sizeof(float2)));
     const std::vector<float2> tw = make_twiddles(N);
-    OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice));
+    OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
+    OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
     for (int i = 0; i < 2; ++i) {
         OCEAN_CUDA(cudaMalloc(&stateDev[i], batch * sizeof(StateConsts)));
         OCEAN_CUDA(cudaMalloc(&seedDev[i], batch * sizeof(uint64_t)));
@@ -402,7 +419,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
     ia.N = N; ia.C = C;
     ia.sc = make_spread_consts();
     for (int i = 0; i < C; ++i) ia.casc[i] = make_cascade_consts(cascades[i]);
-    ia.noise = noise; ia.h0 = h0; ia.wave = wave;
+    ia.noise = noise; ia.h0 = h0; ia.wave = wave; ia.waveHot = waveHot;
     int waveIdx = 0;
     int pendingBase[2] = {-1, -1}, pendingCount[2] = {0, 0};
     auto drain = [&](int b) {
@@ -433,8 +450,9 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         ia.nStates = nb; ia.states = stateDev[b];
         OCEAN_CUDA(launch_init(ia, stream));
         FrameArgs fa{};
-        fa.N = N; fa.layers = nb * C;
-        fa.h0 = h0; fa.wave = wave; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
+        fa.N = N; fa.layers = nb * C; fa.C = C;
+        for (int i = 0; i < C; ++i) fa.dk[i] = ia.casc[i].dk;
+        fa.h0 = h0; fa.waveHot = waveHot; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
         fa.twiddle = twiddle; fa.time = time;
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
@@ -457,7 +475,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
 
 void OceanEnsemble::destroy() {
     if (stream) cudaStreamSynchronize(stream);
-    void* dev[] = {noise, h0, wave, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
+    void* dev[] = {noise, h0, wave, waveHot, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) {
@@ -545,6 +563,13 @@ int ocean_step(OceanHandle* h, float time) {
     if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
     DeviceScope scope(h->device);
     return h->CalculateWavesTexturesAtTime(time);
+}
+
+int ocean_step_partial(OceanHandle* h, float time, int which) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    if (which < 0 || which > 2) return fail(OCEAN_ERR_INVALID_ARGUMENT, "which must be 0, 1 or 2");
+    DeviceScope scope(h->device);
+    return h->CalculateWavesTexturesAtTime(time, which);
 }
 
 int ocean_update(OceanHandle* h, float time) {

@@ -45,14 +45,17 @@ struct InitArgs {
     const StateConsts* states;         // device, nStates entries
     const float2* noise;               // device, [state][y][x]
     float4* h0;                        // device, [state*C + cascade][y][x]
-    float4* wave;
+    float4* wave;                      // (kx, 1/|k|, kz, omega): the reference's waveData layout (inspection / parity)
+    float2* waveHot;                   // (1/|k|, omega): what the frame kernels read; kx, kz are recomputed as n*dk
 };
 
 struct FrameArgs {
     int N;
     int layers;                        // nStates * C
+    int C;                             // cascades per state: cascade of a layer = layer % C
+    float dk[OCEAN_MAX_CASCADES];      // 2*PI/wavelength per cascade (IS:110)
     const float4* h0;
-    const float4* wave;
+    const float2* waveHot;             // (1/|k|, omega) [layer][y][x]
     float4* rowsA;                     // (DxDz, DyDxz) after the x pass, [layer][y][x]
     float4* rowsB;                     // (DyxDyz, DxxDzz)
     float4* disp;

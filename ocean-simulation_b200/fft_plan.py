@@ -31,8 +31,14 @@ def stage_radices(N):
     return r
 
 
-def swizzle(F):
-    """Physical element index (units of one 128-bit element) for logical index F."""
+def swizzle(F, exchange=1, dense0=False):
+    """Physical element index (units of one 128-bit element) for logical index F.
+    A thread's exchange-0 slots (tid + T*q) are exactly the slots of its own 8 input points, so the
+    buffer the inputs are staged in (cp.async, TMA) doubles as the exchange buffer with no barrier.
+    dense0: exchange 0 is unswizzled -- needed when a TMA tensor copy lands the tile in natural order
+    (column kernel); per-thread cp.async (row kernel) can stage straight into swizzled slots."""
+    if exchange == 0 and dense0:
+        return F
     return F ^ ((F >> 3) & 7)
 
 
@@ -42,7 +48,7 @@ def _butterfly(v, r):
     return np.exp(2j * np.pi * np.outer(j, j) / r) @ v
 
 
-def run_plan(x, W=1, check_conflicts=False):
+def run_plan(x, W=1, check_conflicts=False, dense0=False):
     """Transform W interleaved lines.  x: complex array [W][N].  Returns (X[W][N], conflicts).
 
     Lane numbering inside a CTA is lane = xw + W * tid (column index fastest), which is what
@@ -66,7 +72,7 @@ def run_plan(x, W=1, check_conflicts=False):
         if not check_conflicts:
             return
         lane = (np.arange(W)[None, :] + W * tid[:, None]).ravel()
-        phys = swizzle(G.ravel())
+        phys = swizzle(G.ravel(), s, dense0)
         order = np.argsort(lane)
         phys = phys[order]
         worst = 1
@@ -99,7 +105,7 @@ def run_plan(x, W=1, check_conflicts=False):
                 F = (c + Cs * q) * Mn + t
                 G = F[:, None] * W + xw
                 record("write", s, G)
-                smem[swizzle(G)] = u[q]
+                smem[swizzle(G, s, dense0)] = u[q]
             # read for stage s+1
             rn = radices[s + 1]
             Cn = Cs * 8
@@ -110,7 +116,7 @@ def run_plan(x, W=1, check_conflicts=False):
                     F = cn * Mn + tn + (Mn // 8) * j
                     G = F[:, None] * W + xw
                     record("read", s, G)
-                    new.append(smem[swizzle(G)])
+                    new.append(smem[swizzle(G, s, dense0)])
                 reg = np.stack(new)
             else:
                 # last stage with radix rn < 8: thread p handles sub-problems c_i = p + T*i
@@ -120,7 +126,7 @@ def run_plan(x, W=1, check_conflicts=False):
                         F = (tid + T * i) * rn + j  # Mn == rn
                         G = F[:, None] * W + xw
                         record("read", s, G)
-                        new.append(smem[swizzle(G)])
+                        new.append(smem[swizzle(G, s, dense0)])
                 reg = np.stack(new)  # slot i*rn + j
         else:
             # last stage, radix r < 8: 8/r independent butterflies per thread, no twiddle

@@ -131,6 +131,10 @@ class WaterBody:
         """WB:180-193.  Asynchronous; Sync() or any array read waits for it."""
         L.check(self._lib.ocean_step(self._need(), float(time)))
 
+    def StepPartial(self, time, which):
+        """Measurement hook: which = 1 row pass only, 2 column pass + assembly only, 0 both."""
+        L.check(self._lib.ocean_step_partial(self._need(), float(time), int(which)))
+
     def Update(self, time):
         """WB:284-297: one frame + AsyncGPUReadback request of displacement layer 0."""
         L.check(self._lib.ocean_update(self._need(), float(time)))

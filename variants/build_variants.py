@@ -1,0 +1,37 @@
+"""Builds tuning variants of liboceanfft.so (experiments only; not part of the product build).
+Only ocean_frame.cu is recompiled per variant; the other objects come from the product build."""
+import os, re, subprocess, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import oceanpkg
+HERE = os.path.dirname(os.path.abspath(__file__))
+VARIANTS = {
+    "base": [],
+
+    "cw4_m3": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=3", "-DOCEAN_COLS512_DB=true"],
+    "cw4_m3s": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=3"],
+    "cw4_m2": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=2", "-DOCEAN_COLS512_DB=true"],
+    "cw8_m1": ["-DOCEAN_COLS512_W=8", "-DOCEAN_COLS512_MINB=1", "-DOCEAN_COLS512_DB=true"],
+    "cw8_m2": ["-DOCEAN_COLS512_W=8", "-DOCEAN_COLS512_MINB=2"],
+    "cw2_m5": ["-DOCEAN_COLS512_MINB=5", "-DOCEAN_COLS512_DB=true"],
+    "cw2_m4": ["-DOCEAN_COLS512_MINB=4", "-DOCEAN_COLS512_DB=true"],
+    "r_m10": ["-DOCEAN_ROWS512_MINB=10", "-DOCEAN_ROWS512_DB=true"],
+    "r_m8": ["-DOCEAN_ROWS512_MINB=8", "-DOCEAN_ROWS512_DB=true"],
+    "r2_m5": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=5", "-DOCEAN_ROWS512_DB=true"],
+    "r2_m7": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
+    "r4_m2": ["-DOCEAN_ROWS512_R=4", "-DOCEAN_ROWS512_MINB=2", "-DOCEAN_ROWS512_DB=true"],
+}
+if __name__ == "__main__":
+    bm = oceanpkg.build_module()
+    bm.build()
+    names = sys.argv[1:] or list(VARIANTS)
+    for n in names:
+        obj = os.path.join(HERE, "frame_%s.o" % n)
+        cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + bm.COMMON + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
+        info = re.findall(r"ocean_(rows|cols)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
+        others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o")]
+        subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", os.path.join(HERE, "lib_%s.so" % n), obj] + others)
+        os.remove(obj)
+        print(n, info, flush=True)
