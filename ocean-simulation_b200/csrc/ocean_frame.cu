@@ -15,6 +15,7 @@
 
 #include "ocean_fft.cuh"
 #include "ocean_internal.h"
+#include "ocean_tma.cuh"
 
 namespace ocean {
 
@@ -214,6 +215,136 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 }
 
 // ---------------------------------------------------------------------------------------------
+// Column pass, TMA version (N = 256, 512): persistent CTAs, one tile = W adjacent columns.
+//
+//   * each of the two packed-spectra pairs of a tile is fetched by TMA tensor copies (boxes of
+//     4W floats x 256 rows) that land in natural [y][x] order in a shared-memory buffer;
+//   * that buffer IS exchange 0 of the FFT (DENSE0): thread (tid, xw) reads exactly the 8 points it
+//     later overwrites, so no barrier separates staging from the transform;
+//   * pair B, the turbulence texels and the next tile's pair A are in flight while pair A is
+//     transformed, so HBM/L2 latency is off the critical path after the first tile;
+//   * results leave through 128-bit streaming stores, W*16 contiguous bytes per row.
+#ifndef OCEAN_COLS512_TMA_W
+#define OCEAN_COLS512_TMA_W 8
+#endif
+#ifndef OCEAN_COLS512_TMA_MINB
+#define OCEAN_COLS512_TMA_MINB 1
+#endif
+
+template <int N> struct ColTmaCfg {
+    static constexpr int T = N / 8;
+    static constexpr int W = (N == 512) ? OCEAN_COLS512_TMA_W : 8;
+    static constexpr int THREADS = W * T;
+    static constexpr int MINB = (N == 512) ? OCEAN_COLS512_TMA_MINB : 2;
+    static constexpr int BOX_ROWS = N < 256 ? N : 256;
+    static constexpr int NBOX = N / BOX_ROWS;
+    static constexpr int TILE_ELEMS = N * W;                    // float4 per pair-tile
+    static constexpr int SMEM_BYTES = 2 * TILE_ELEMS * 16 + 64; // two pair buffers + mbarriers
+    using FFT = LineFFT<N, W, true, false, true>;
+};
+
+template <int N>
+__global__ void __launch_bounds__(ColTmaCfg<N>::THREADS, ColTmaCfg<N>::MINB)
+ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const FrameArgs a,
+                      const int totalTiles) {
+    using Cfg = ColTmaCfg<N>;
+    using FFT = typename Cfg::FFT;
+    constexpr int T = Cfg::T, W = Cfg::W, TILES_PER_LAYER = N / W;
+    extern __shared__ __align__(128) float4 smem[];
+    float4* bufA = smem;
+    float4* bufB = smem + Cfg::TILE_ELEMS;
+    uint64_t* bars = (uint64_t*)(smem + 2 * Cfg::TILE_ELEMS);  // [0] pair A, [1] pair B
+    const int xw = threadIdx.x & (W - 1);
+    const int tid = threadIdx.x / W;
+
+    auto issue = [&](const CUtensorMap* map, float4* buf, uint64_t* bar, int tile) {
+        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
+        mbar_arrive_expect_tx(bar, Cfg::TILE_ELEMS * 16);
+#pragma unroll
+        for (int b = 0; b < Cfg::NBOX; ++b)
+            tma_load_2d(buf + b * Cfg::BOX_ROWS * W, map, bar, xt * W * 4, layer * N + b * Cfg::BOX_ROWS);
+    };
+
+    int tile = blockIdx.x;
+    if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+        if (tile < totalTiles) {
+            issue(&mapA, bufA, &bars[0], tile);
+            issue(&mapB, bufB, &bars[1], tile);
+        }
+    }
+    __syncthreads();
+
+    const float lambda = a.lambda, decay = a.foamDecay;
+    const bool zeroFoam = a.zeroFoam != 0;
+    uint32_t parity = 0;
+    for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
+        const int next = tile + gridDim.x;
+        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
+        const int x = xt * W + xw;
+        const size_t base = (size_t)layer * N * N + x;  // texel (x, 0) of this layer
+        // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
+        const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
+        float4 r[8];
+        float dxz[8], foam[8];
+
+        // ---- pair A = (DxDz, DyDxz) -> displacement -------------------------------------------
+        mbar_wait(&bars[0], parity);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = bufA[(tid + T * j) * W + xw];
+        FFT::run(r, bufA, tid, xw, a.twiddle, 0);
+        __syncthreads();  // every thread has finished reading bufA
+        if (threadIdx.x == 0 && next < totalTiles) {
+            fence_proxy_async();
+            issue(&mapA, bufA, &bars[0], next);
+        }
+        // turbulence of this tile: issued now, consumed after pair B's transform (RF:28)
+        {
+            const float4* __restrict__ turb = a.turb + base;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) foam[j] = zeroFoam ? 0.0f : __ldcs(&turb[(size_t)(tid + T * j) * N].x);
+        }
+        {
+            float4* __restrict__ disp = a.disp + base;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                // r = (DxDz, DyDxz) * sign;  displacement = (Dx, Dy, Dz)  RF:25 (alpha := 0)
+                const float dx = r[j].x * sgn, dz = r[j].y * sgn, dy = r[j].z * sgn;
+                dxz[j] = r[j].w * sgn * lambda;
+                st_stream(disp + (size_t)(tid + T * j) * N, make_float4(dx * lambda, dy, dz * lambda, 0.0f));
+            }
+        }
+        // ---- pair B = (DyxDyz, DxxDzz) -> derivatives, Jacobian, foam --------------------------
+        mbar_wait(&bars[1], parity);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = bufB[(tid + T * j) * W + xw];
+        FFT::run(r, bufB, tid, xw, a.twiddle, 0);
+        __syncthreads();
+        if (threadIdx.x == 0 && next < totalTiles) {
+            fence_proxy_async();
+            issue(&mapB, bufB, &bars[1], next);
+        }
+        {
+            float4* __restrict__ deriv = a.deriv + base;
+            float4* __restrict__ turb = a.turb + base;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const size_t o = (size_t)(tid + T * j) * N;
+                const float dyx = r[j].x * sgn, dyz = r[j].y * sgn;                      // RF:26
+                const float dxx = r[j].z * sgn * lambda, dzz = r[j].w * sgn * lambda;
+                st_stream(deriv + o, make_float4(dyx, dyz, dxx, dzz));
+                const float jac = (1.0f + dxx) * (1.0f + dzz) - dxz[j] * dxz[j];         // RF:27
+                float f = foam[j] * decay;                                               // RF:28-30
+                if (f < jac) f += jac;                                                   // RF:31
+                st_stream(turb + o, make_float4(f, f, f, f));                            // RF:32
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // WaterBody.GetWaterHeight WB:195-209 (mode 0), plus bilinear extensions at the shader's own
 // mapping uv = worldXZ / wavelength (Water.shader:325) with Repeat wrap.
 struct QueryArgs {
@@ -297,6 +428,75 @@ template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t
     count_launch();
     return cudaGetLastError();
 }
+
+static int g_numSMs = 0;
+static int num_sms() {
+    if (g_numSMs == 0) {
+        int dev = 0, n = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        g_numSMs = n > 0 ? n : 148;
+    }
+    return g_numSMs;
+}
+
+template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const ColsTmaMaps& m, cudaStream_t s) {
+    using Cfg = ColTmaCfg<N>;
+    const int totalTiles = a.layers * (N / Cfg::W);
+    static int ctasPerSM = 0;  // resident CTAs per SM for this kernel: the persistent grid size
+    if (ctasPerSM == 0) {
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_cols_tma_kernel<N>, Cfg::THREADS, Cfg::SMEM_BYTES);
+        ctasPerSM = n > 0 ? n : 1;
+    }
+    const int slots = num_sms() * ctasPerSM;
+    const int grid = totalTiles < slots ? totalTiles : slots;
+    ocean_cols_tma_kernel<N><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(m.a, m.b, a, totalTiles);
+    count_launch();
+    return cudaGetLastError();
+}
+template <int N> static cudaError_t configure_tma() {
+    cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaSuccess;
+}
+static bool tma_size(int N) { return N == 256 || N == 512; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, ColsTmaMaps* out) {
+    out->valid = 0;
+    if (!tma_size(N)) return cudaSuccess;
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess) return e;
+        if (!fn || q != cudaDriverEntryPointSuccess) return cudaErrorNotSupported;
+        encode = (EncodeTiledFn)fn;
+    }
+    const int W = N == 512 ? ColTmaCfg<512>::W : ColTmaCfg<256>::W;
+    const int boxRows = N < 256 ? N : 256;
+    const cuuint64_t dims[2] = {(cuuint64_t)N * 4, (cuuint64_t)layers * N};  // fp32 elements per row, rows
+    const cuuint64_t strides[1] = {(cuuint64_t)N * 16};                      // bytes between rows
+    const cuuint32_t box[2] = {(cuuint32_t)W * 4, (cuuint32_t)boxRows};
+    const cuuint32_t estr[2] = {1, 1};
+    const float4* ptrs[2] = {rowsA, rowsB};
+    CUtensorMap* maps[2] = {&out->a, &out->b};
+    for (int i = 0; i < 2; ++i) {
+        CUresult r = encode(maps[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptrs[i], dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    }
+    out->valid = 1;
+    return cudaSuccess;
+}
+
 template <int N> static cudaError_t configure() {
     cudaError_t e = cudaFuncSetAttribute(ocean_rows_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, RowCfg<N>::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -308,7 +508,16 @@ template <int N> static cudaError_t configure() {
     return cudaSuccess;
 }
 template <int N> static const char* describe() {
-    static char buf[256];
+    static char buf[512];
+    if (N == 512 || N == 256) {
+        constexpr int M = (N == 512 || N == 256) ? N : 512;
+        snprintf(buf, sizeof buf,
+                 "rows<N=%d>: %d rows/CTA, %d threads, %d B smem (cp.async-staged row = exchange buffer); "
+                 "cols_tma<N=%d>: persistent, %d columns/tile, %d threads, %d B smem (TMA-staged tile = exchange buffer)",
+                 N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::SMEM_BYTES, N, ColTmaCfg<M>::W, ColTmaCfg<M>::THREADS,
+                 ColTmaCfg<M>::SMEM_BYTES);
+        return buf;
+    }
     snprintf(buf, sizeof buf,
              "rows<N=%d>: %d rows/CTA, %d threads, %d B smem, %s buffer; cols<N=%d>: %d columns/CTA, %d threads, %d B smem, %s buffer",
              N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::SMEM_BYTES, "single", N,
@@ -335,13 +544,19 @@ cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s) {
 #undef CALL
     return cudaErrorInvalidValue;
 }
-cudaError_t launch_cols(const FrameArgs& a, cudaStream_t s) {
+cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s) {
+    if (maps && maps->valid) {
+        if (a.N == 512) return cols_tma_launch<512>(a, *maps, s);
+        if (a.N == 256) return cols_tma_launch<256>(a, *maps, s);
+    }
 #define CALL(n) cols_launch<n>(a, s)
     OCEAN_DISPATCH_N(a.N, CALL)
 #undef CALL
     return cudaErrorInvalidValue;
 }
 cudaError_t configure_frame_kernels(int N) {
+    if (N == 512) { cudaError_t e = configure_tma<512>(); if (e != cudaSuccess) return e; }
+    if (N == 256) { cudaError_t e = configure_tma<256>(); if (e != cudaSuccess) return e; }
 #define CALL(n) configure<n>()
     OCEAN_DISPATCH_N(N, CALL)
 #undef CALL

@@ -159,6 +159,7 @@ struct OceanHandle {
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr;
     float4 *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     float2* waveHot = nullptr;  // (1/|k|, omega): compact copy of waveData read by the frame kernels
+    ColsTmaMaps colsMaps;       // TMA descriptors over rowsA / rowsB
     float2* twiddle = nullptr;
     StateConsts* stateDev = nullptr;
     uint64_t* seedDev = nullptr;
@@ -221,6 +222,7 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
         OCEAN_CUDA(launch_noise(seedDev, 1, N, noise, stream));
     }
     OCEAN_CUDA(configure_frame_kernels(N));
+    OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, &colsMaps));
     for (int i = 0; i < RB; ++i) {
         OCEAN_CUDA(cudaMalloc(&rbStage[i], layerBytes4()));
         OCEAN_CUDA(cudaMallocHost(&rbHost[i], layerBytes4()));
@@ -257,7 +259,7 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     a.zeroFoam = foamZero ? 1 : 0;
     if (which == 0 || which == 1) OCEAN_CUDA(launch_rows(a, stream));
     if (which == 0 || which == 2) {
-        OCEAN_CUDA(launch_cols(a, stream));
+        OCEAN_CUDA(launch_cols(a, &colsMaps, stream));
         foamZero = false;
         ++frame;
     }
@@ -374,6 +376,7 @@ struct OceanEnsemble {
     float2* noise = nullptr;
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     float2* waveHot = nullptr;
+    ColsTmaMaps colsMaps;
     float2* twiddle = nullptr;
     // double-buffered parameter / result staging so consecutive waves overlap
     StateConsts* stateDev[2] = {nullptr, nullptr};
@@ -411,6 +414,7 @@ int OceanEnsemble::create() {
         OCEAN_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
     }
     OCEAN_CUDA(configure_frame_kernels(N));
+    OCEAN_CUDA(make_cols_maps(N, batch * C, rowsA, rowsB, &colsMaps));
     return OCEAN_OK;
 }
 
@@ -458,7 +462,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
         OCEAN_CUDA(launch_rows(fa, stream));
-        OCEAN_CUDA(launch_cols(fa, stream));
+        OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
         OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
         OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
         OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));

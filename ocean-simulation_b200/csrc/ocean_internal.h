@@ -2,6 +2,7 @@
 // (ocean_init.cu is built with -fmad=false so that the one-time spectrum follows the
 // reference's operation order rounding for rounding; ocean_frame.cu keeps FMA contraction.)
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -68,11 +69,21 @@ struct FrameArgs {
     int zeroFoam;                      // 1: treat the incoming turbulence as zero (fresh texture)
 };
 
+// TMA descriptors of the two intermediate planes, viewed as 2-D fp32 tensors {4N, layers*N}; the
+// column kernel loads a tile of W adjacent columns (4W floats x up to 256 rows per box) with them.
+struct ColsTmaMaps {
+    CUtensorMap a, b;
+    int valid = 0;
+};
+// Encodes the maps (driver entry point fetched through the runtime: no libcuda link).  Leaves
+// valid = 0 for sizes the TMA column kernel does not cover; those use the generic column kernel.
+cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, ColsTmaMaps* out);
+
 // launchers (return cudaGetLastError()); every launch bumps the launch counter
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
 cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s);
-cudaError_t launch_cols(const FrameArgs& a, cudaStream_t s);
+cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
