@@ -12,6 +12,9 @@
 // read that 32 (L2-resident) + turbulence 16 and write 3 x 16.  Algorithmic = 96 B.
 // Bandwidth-bound fp32 FFT: tensor cores are not used (no dense contraction here).
 #include <stdio.h>
+#include <stdlib.h>
+
+#include <utility>
 
 #include "ocean_fft.cuh"
 #include "ocean_internal.h"
@@ -38,6 +41,14 @@ __device__ __forceinline__ void cp_async8(void* smemDst, const void* g) {
 __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
+
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
+// attribute may begin while its predecessor in the stream is still running.  pdl_trigger() lets the
+// successor start early; pdl_wait() blocks until every predecessor grid has completed and flushed.
+// Both kernels of a frame call pdl_wait() before touching anything a predecessor kernel writes or
+// reads-and-we-overwrite, so completion stays transitive along the stream.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // tuning knobs for the headline size (overridable at build time for experiments)
 #ifndef OCEAN_ROWS512_R
@@ -95,6 +106,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (!active) line = totalRows - 1;  // keep every thread in the barriers; results are dropped
     const float4* __restrict__ H = a.h0 + line * N;
     const float2* __restrict__ Wd = a.waveHot + line * N;
+    pdl_trigger();
 
     // Stage the whole row: 16 asynchronous copies per thread are in flight before any arithmetic.
     // Element x lands in the slot exchange 0 will later use for it, and thread `tid` only ever
@@ -140,6 +152,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     }
 
     FFT::run(pa, smem, tid, row, a.twiddle, 0);
+    // h0 / waveHot are never written by a frame kernel, so everything above may overlap the previous
+    // frame's column pass; the intermediate planes it is still reading may only be overwritten now.
+    pdl_wait();
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
 #pragma unroll
@@ -164,6 +179,8 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     const int tid = threadIdx.x / W;
     const int x = blockIdx.x * W + xw;
     const size_t base = (size_t)blockIdx.y * N * N + x;  // texel (x, 0) of this layer
+    pdl_trigger();
+    pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
     const float lambda = a.lambda;
     // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
     const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
@@ -266,10 +283,14 @@ ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_con
     };
 
     int tile = blockIdx.x;
+    pdl_trigger();
     if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
         mbar_fence_init();
+    }
+    pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
+    if (threadIdx.x == 0) {
         if (tile < totalTiles) {
             issue(&mapA, bufA, &bars[0], tile);
             issue(&mapB, bufB, &bars[1], tile);
@@ -413,20 +434,36 @@ __global__ void ocean_checksum_kernel(const uint4* __restrict__ arr, size_t floa
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t s) {
+// Launch with programmatic stream serialization (PDL) unless OCEAN_NO_PDL is set in the environment.
+static bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) v = getenv("OCEAN_NO_PDL") ? 0 : 1;
+    return v != 0;
+}
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(bool early, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smemBytes, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smemBytes; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (early && pdl_enabled()) ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+    count_launch();
+    return e;
+}
+
+template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t s, bool early) {
     using Cfg = RowCfg<N>;
     const size_t totalRows = (size_t)a.layers * N;
     const unsigned grid = (unsigned)((totalRows + Cfg::R - 1) / Cfg::R);
-    ocean_rows_kernel<N><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(a);
-    count_launch();
-    return cudaGetLastError();
+    return launch_pdl(early, ocean_rows_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, a);
 }
 template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t s) {
     using Cfg = ColCfg<N>;
     dim3 grid(N / Cfg::W, a.layers);
-    ocean_cols_kernel<N><<<grid, Cfg::THREADS, Cfg::FFT::SMEM_BYTES, s>>>(a);
-    count_launch();
-    return cudaGetLastError();
+    return launch_pdl(true, ocean_cols_kernel<N>, grid, dim3(Cfg::THREADS), Cfg::FFT::SMEM_BYTES, s, a);
 }
 
 static int g_numSMs = 0;
@@ -451,9 +488,7 @@ template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const Co
     }
     const int slots = num_sms() * ctasPerSM;
     const int grid = totalTiles < slots ? totalTiles : slots;
-    ocean_cols_tma_kernel<N><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(m.a, m.b, a, totalTiles);
-    count_launch();
-    return cudaGetLastError();
+    return launch_pdl(true, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m.a, m.b, a, totalTiles);
 }
 template <int N> static cudaError_t configure_tma() {
     cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
@@ -538,8 +573,8 @@ template <int N> static const char* describe() {
         default: break;                            \
     }
 
-cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s) {
-#define CALL(n) rows_launch<n>(a, s)
+cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early) {
+#define CALL(n) rows_launch<n>(a, s, early)
     OCEAN_DISPATCH_N(a.N, CALL)
 #undef CALL
     return cudaErrorInvalidValue;

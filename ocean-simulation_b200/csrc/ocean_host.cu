@@ -257,7 +257,7 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     a.time = time; a.lambda = params.lambda;
     a.foamDecay = expf(-2.0f);  // RF:29-30
     a.zeroFoam = foamZero ? 1 : 0;
-    if (which == 0 || which == 1) OCEAN_CUDA(launch_rows(a, stream));
+    if (which == 0 || which == 1) OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
     if (which == 0 || which == 2) {
         OCEAN_CUDA(launch_cols(a, &colsMaps, stream));
         foamZero = false;
@@ -461,7 +461,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
-        OCEAN_CUDA(launch_rows(fa, stream));
+        OCEAN_CUDA(launch_rows(fa, stream, false));  // follows the init kernel: no early start
         OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
         OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
         OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));

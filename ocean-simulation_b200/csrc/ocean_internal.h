@@ -82,7 +82,9 @@ cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4*
 // launchers (return cudaGetLastError()); every launch bumps the launch counter
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
 cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
-cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s);
+// early: the row pass may start before the previous kernel in the stream has finished (PDL).  Only
+// legal when that kernel does not produce h0 / waveHot / twiddles (i.e. it is a column pass).
+cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early);
 cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);

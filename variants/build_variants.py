@@ -7,19 +7,14 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-
-    "cw4_m3": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=3", "-DOCEAN_COLS512_DB=true"],
-    "cw4_m3s": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=3"],
-    "cw4_m2": ["-DOCEAN_COLS512_W=4", "-DOCEAN_COLS512_MINB=2", "-DOCEAN_COLS512_DB=true"],
-    "cw8_m1": ["-DOCEAN_COLS512_W=8", "-DOCEAN_COLS512_MINB=1", "-DOCEAN_COLS512_DB=true"],
-    "cw8_m2": ["-DOCEAN_COLS512_W=8", "-DOCEAN_COLS512_MINB=2"],
-    "cw2_m5": ["-DOCEAN_COLS512_MINB=5", "-DOCEAN_COLS512_DB=true"],
-    "cw2_m4": ["-DOCEAN_COLS512_MINB=4", "-DOCEAN_COLS512_DB=true"],
-    "r_m10": ["-DOCEAN_ROWS512_MINB=10", "-DOCEAN_ROWS512_DB=true"],
-    "r_m8": ["-DOCEAN_ROWS512_MINB=8", "-DOCEAN_ROWS512_DB=true"],
-    "r2_m5": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=5", "-DOCEAN_ROWS512_DB=true"],
+    "tw4_m3": ["-DOCEAN_COLS512_TMA_W=4", "-DOCEAN_COLS512_TMA_MINB=3"],
+    "tw4_m2": ["-DOCEAN_COLS512_TMA_W=4", "-DOCEAN_COLS512_TMA_MINB=2"],
+    "tw2_m6": ["-DOCEAN_COLS512_TMA_W=2", "-DOCEAN_COLS512_TMA_MINB=6"],
+    "r_m12": ["-DOCEAN_ROWS512_MINB=12"],
+    "r_m10": ["-DOCEAN_ROWS512_MINB=10"],
+    "r_m7": ["-DOCEAN_ROWS512_MINB=7"],
     "r2_m7": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
-    "r4_m2": ["-DOCEAN_ROWS512_R=4", "-DOCEAN_ROWS512_MINB=2", "-DOCEAN_ROWS512_DB=true"],
+    "r2_m4": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=4"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
@@ -30,7 +25,7 @@ if __name__ == "__main__":
         cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + bm.COMMON + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
-        info = re.findall(r"ocean_(rows|cols)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
+        info = re.findall(r"ocean_(rows|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
         others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o")]
         subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", os.path.join(HERE, "lib_%s.so" % n), obj] + others)
         os.remove(obj)
