@@ -5,6 +5,7 @@ repo-root helper:  `import oceanpkg; pkg = oceanpkg.load()`  ->  pkg.WaterBody, 
 """
 from . import _lib
 from . import scene
+from . import sharding
 from .waterbody import OceanEnsemble, WaterBody, WaterCascade
 
-__all__ = ["WaterBody", "WaterCascade", "OceanEnsemble", "scene", "_lib"]
+__all__ = ["WaterBody", "WaterCascade", "OceanEnsemble", "scene", "sharding", "_lib"]

@@ -30,8 +30,9 @@ def po():
 
 
 def rel_l2(a, b):
-    a = np.asarray(a, np.float64)
-    b = np.asarray(b, np.float64)
+    cplx = np.iscomplexobj(a) or np.iscomplexobj(b)
+    a = np.asarray(a, np.complex128 if cplx else np.float64)
+    b = np.asarray(b, np.complex128 if cplx else np.float64)
     d = np.linalg.norm(b.ravel())
     return float(np.linalg.norm((a - b).ravel()) / d) if d > 0 else float(np.linalg.norm((a - b).ravel()))
 
