@@ -82,8 +82,9 @@ typedef enum OceanArray {
     OCEAN_INITIAL_SPECTRUM = 3, /* RGBA32F (h0(k), conj h0(-k))  initialSpectrumTextures WB:37, IS:120,141 */
     OCEAN_WAVES_DATA = 4,       /* RGBA32F (kx, 1/|k|, kz, omega) wavesDataTextures      WB:38, IS:123 */
     OCEAN_NOISE = 5,            /* RG32F, one layer, shared by all cascades      randomNoiseTexture WB:34 */
-    OCEAN_ROW_SPECTRA = 6       /* debug: state between the x and y passes, 2 planes of RGBA32F:
-                                   plane 0 = (DxDz, DyDxz), plane 1 = (DyxDyz, DxxDzz), each [layer][y][x] */
+    OCEAN_ROW_SPECTRA = 6       /* debug: state between the x and y passes, 2 planes of RGBA32F, each [layer][y][x]:
+                                   plane 0 = spectra (DxDz, DyDxz), plane 1 = (DyxDyz, DxxDzz), a texel holding
+                                   (re of first, re of second, im of first, im of second) */
 } OceanArray;
 
 typedef enum OceanQueryMode {

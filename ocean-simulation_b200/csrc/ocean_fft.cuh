@@ -9,67 +9,110 @@
 // The index algebra is restated and proven against numpy in ocean-simulation_b200/fft_plan.py
 // (tests/test_fft_plan.py); keep the two in step.
 //
-// Each element is a float4 = two packed complex spectra (xy, zw), so one exchange moves a pair
-// of the reference's four packed spectra (TD:42-45) and every shared-memory access is 128-bit.
+// Element type: C2 = TWO complex values, one from each of two packed spectra (TD:42-45), held
+// structure-of-arrays as two 64-bit register pairs  re = (re_a, re_b), im = (im_a, im_b).  Every
+// butterfly, rotation and twiddle multiplication is then element-wise on a pair, which is exactly
+// what Blackwell's packed fp32 instructions do (PTX add/sub/mul/fma .f32x2 -> SASS FADD2 / FMUL2 /
+// FFMA2, sm_100+): one issue slot per two flops-lanes, halving the FP instruction count of the
+// transform.  A twiddle (wx, wy) multiplies both spectra, so it enters as a scalar broadcast
+// operand (ptxas emits the .F32 broadcast form; negations fold into operand modifiers).
+// In memory a C2 is one 128-bit element (re_a, re_b, im_a, im_b).
 #pragma once
 #include <cuda_runtime.h>
 
 namespace ocean {
 
-__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
-    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+typedef unsigned long long u64;
+
+__device__ __forceinline__ u64 pk2(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
 }
+__device__ __forceinline__ float lo2(u64 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return a;
+}
+__device__ __forceinline__ float hi2(u64 v) {
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return b;
+}
+__device__ __forceinline__ u64 bc2(float s) { return pk2(s, s); }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) {
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 neg2(u64 a) { return pk2(-lo2(a), -hi2(a)); }  // folds into operand modifiers
+
+struct C2 {
+    u64 re, im;
+};
+__device__ __forceinline__ C2 operator+(const C2& a, const C2& b) { return C2{add2(a.re, b.re), add2(a.im, b.im)}; }
+__device__ __forceinline__ C2 operator-(const C2& a, const C2& b) { return C2{sub2(a.re, b.re), sub2(a.im, b.im)}; }
+__device__ __forceinline__ C2 mul_i(const C2& a) { return C2{neg2(a.im), a.re}; }  // a * i
+// both spectra times the same complex scalar w
+__device__ __forceinline__ C2 cmul(const C2& a, float2 w) {
+    const u64 wx = bc2(w.x), wy = bc2(w.y);
+    return C2{fma2(a.re, wx, neg2(mul2(a.im, wy))), fma2(a.re, wy, mul2(a.im, wx))};
+}
+__device__ __forceinline__ C2 c2_from(const float4& v) { return C2{pk2(v.x, v.y), pk2(v.z, v.w)}; }
+__device__ __forceinline__ float4 c2_to(const C2& v) { return make_float4(lo2(v.re), hi2(v.re), lo2(v.im), hi2(v.im)); }
+__device__ __forceinline__ C2 c2_load(const float4* p) {
+    const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p);
+    return C2{v.x, v.y};
+}
+__device__ __forceinline__ void c2_store(float4* p, const C2& v) { *reinterpret_cast<ulonglong2*>(p) = make_ulonglong2(v.re, v.im); }
 
 #define OCEAN_SQRT1_2 0.70710678118654752440f
 
-// u[q] = sum_j v[j] e^{+2 pi i j q / 8}, in place, natural order; both packed spectra at once.
-__device__ __forceinline__ void radix8_inv(float4 (&v)[8]) {
-    float4 a[4], b[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        a[j] = make_float4(v[j].x + v[j + 4].x, v[j].y + v[j + 4].y, v[j].z + v[j + 4].z, v[j].w + v[j + 4].w);
-        b[j] = make_float4(v[j].x - v[j + 4].x, v[j].y - v[j + 4].y, v[j].z - v[j + 4].z, v[j].w - v[j + 4].w);
-    }
-    // b[j] *= e^{+i pi j / 4}
-    {
-        float4 t = b[1];  // * (1+i)/sqrt2
-        b[1] = make_float4((t.x - t.y) * OCEAN_SQRT1_2, (t.x + t.y) * OCEAN_SQRT1_2,
-                           (t.z - t.w) * OCEAN_SQRT1_2, (t.z + t.w) * OCEAN_SQRT1_2);
-        t = b[2];  // * i
-        b[2] = make_float4(-t.y, t.x, -t.w, t.z);
-        t = b[3];  // * (-1+i)/sqrt2
-        b[3] = make_float4((-t.x - t.y) * OCEAN_SQRT1_2, (t.x - t.y) * OCEAN_SQRT1_2,
-                           (-t.z - t.w) * OCEAN_SQRT1_2, (t.z - t.w) * OCEAN_SQRT1_2);
-    }
-    // two inverse DFT-4: a -> even outputs, b -> odd outputs
-#define OCEAN_DFT4(c, o0, o1, o2, o3)                                                                   \
-    {                                                                                                   \
-        float4 e0 = make_float4(c[0].x + c[2].x, c[0].y + c[2].y, c[0].z + c[2].z, c[0].w + c[2].w);    \
-        float4 e1 = make_float4(c[1].x + c[3].x, c[1].y + c[3].y, c[1].z + c[3].z, c[1].w + c[3].w);    \
-        float4 d0 = make_float4(c[0].x - c[2].x, c[0].y - c[2].y, c[0].z - c[2].z, c[0].w - c[2].w);    \
-        /* d1 = i * (c1 - c3) */                                                                        \
-        float4 d1 = make_float4(-(c[1].y - c[3].y), c[1].x - c[3].x, -(c[1].w - c[3].w), c[1].z - c[3].z); \
-        v[o0] = make_float4(e0.x + e1.x, e0.y + e1.y, e0.z + e1.z, e0.w + e1.w);                        \
-        v[o2] = make_float4(e0.x - e1.x, e0.y - e1.y, e0.z - e1.z, e0.w - e1.w);                        \
-        v[o1] = make_float4(d0.x + d1.x, d0.y + d1.y, d0.z + d1.z, d0.w + d1.w);                        \
-        v[o3] = make_float4(d0.x - d1.x, d0.y - d1.y, d0.z - d1.z, d0.w - d1.w);                        \
-    }
-    OCEAN_DFT4(a, 0, 2, 4, 6)
-    OCEAN_DFT4(b, 1, 3, 5, 7)
-#undef OCEAN_DFT4
+// Inverse DFT-4: o[q] = sum_j c[j] e^{+2 pi i j q / 4}
+__device__ __forceinline__ void radix4_inv(const C2& c0, const C2& c1, const C2& c2, const C2& c3, C2& o0, C2& o1, C2& o2, C2& o3) {
+    const C2 e0 = c0 + c2, e1 = c1 + c3, d0 = c0 - c2, t = c1 - c3;
+    o0 = e0 + e1;
+    o2 = e0 - e1;
+    // d1 = i * t = (-t.im, t.re)
+    o1 = C2{sub2(d0.re, t.im), add2(d0.im, t.re)};
+    o3 = C2{add2(d0.re, t.im), sub2(d0.im, t.re)};
 }
 
-// Inverse DFT-4 of v[base + 0..3] -> out[0..3]
-__device__ __forceinline__ void radix4_inv(const float4& c0, const float4& c1, const float4& c2, const float4& c3,
-                                           float4& o0, float4& o1, float4& o2, float4& o3) {
-    float4 e0 = make_float4(c0.x + c2.x, c0.y + c2.y, c0.z + c2.z, c0.w + c2.w);
-    float4 e1 = make_float4(c1.x + c3.x, c1.y + c3.y, c1.z + c3.z, c1.w + c3.w);
-    float4 d0 = make_float4(c0.x - c2.x, c0.y - c2.y, c0.z - c2.z, c0.w - c2.w);
-    float4 d1 = make_float4(-(c1.y - c3.y), c1.x - c3.x, -(c1.w - c3.w), c1.z - c3.z);
-    o0 = make_float4(e0.x + e1.x, e0.y + e1.y, e0.z + e1.z, e0.w + e1.w);
-    o2 = make_float4(e0.x - e1.x, e0.y - e1.y, e0.z - e1.z, e0.w - e1.w);
-    o1 = make_float4(d0.x + d1.x, d0.y + d1.y, d0.z + d1.z, d0.w + d1.w);
-    o3 = make_float4(d0.x - d1.x, d0.y - d1.y, d0.z - d1.z, d0.w - d1.w);
+// u[q] = sum_j v[j] e^{+2 pi i j q / 8}, in place, natural order; both packed spectra at once.
+__device__ __forceinline__ void radix8_inv(C2 (&v)[8]) {
+    C2 a[4], b[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        a[j] = v[j] + v[j + 4];
+        b[j] = v[j] - v[j + 4];
+    }
+    // b[j] *= e^{+i pi j / 4}
+    const u64 c = bc2(OCEAN_SQRT1_2);
+    {
+        C2 t = b[1];  // * (1+i)/sqrt2
+        b[1] = C2{mul2(sub2(t.re, t.im), c), mul2(add2(t.re, t.im), c)};
+        b[2] = mul_i(b[2]);
+        t = b[3];  // * (-1+i)/sqrt2
+        b[3] = C2{mul2(neg2(add2(t.re, t.im)), c), mul2(sub2(t.re, t.im), c)};
+    }
+    // two inverse DFT-4: a -> even outputs, b -> odd outputs
+    radix4_inv(a[0], a[1], a[2], a[3], v[0], v[2], v[4], v[6]);
+    radix4_inv(b[0], b[1], b[2], b[3], v[1], v[3], v[5], v[7]);
 }
 
 constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
@@ -82,18 +125,19 @@ constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
 //
 // Twiddles: table tw[(s*7 + q-1)*T + tid] = e^{+2 pi i t q C_s / N}, t = tid mod (M_s/8), one entry
 // per (stage, q, thread) so that a warp reads 32 consecutive float2 (see make_twiddles, ocean_host.cu).
-template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF, bool DENSE0 = false>
+// The table may live in global memory (read-only path) or in shared memory (persistent kernels).
+template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF, bool DENSE0 = false, bool TW_SMEM = false>
 struct LineFFT {
     static constexpr int T = N / 8;
     static constexpr int LOGN = ilog2(N);
     static constexpr int S = (LOGN + 2) / 3;             // stages: 8,8,...,RLAST
     static constexpr int RLAST = N >> (3 * (S - 1));     // 2, 4 or 8
     static constexpr int EXCHANGES = S - 1;
-    static constexpr int BUF_ELEMS = N * NL;             // float4 elements per buffer
+    static constexpr int BUF_ELEMS = N * NL;             // 128-bit elements per buffer
     static constexpr int SMEM_BYTES = BUF_ELEMS * 16 * (DOUBLE_BUF ? 2 : 1);
     static_assert(N >= 16 && (N & (N - 1)) == 0, "N must be a power of two >= 16");
 
-    // logical element F of line `ln` -> physical float4 index; XOR swizzle keeps every 128-bit
+    // logical element F of line `ln` -> physical 128-bit index; XOR swizzle keeps every 128-bit
     // access of a quarter-warp on 8 distinct 16-byte bank groups (checked in fft_plan.py)
     template <int s>
     __device__ static __forceinline__ int phys(int F, int ln) {
@@ -103,8 +147,13 @@ struct LineFFT {
     }
     static constexpr int TWIDDLE_ENTRIES = (S - 1) * 7 * T;
 
+    __device__ static __forceinline__ float2 twiddle(const float2* __restrict__ tw, int i) {
+        if constexpr (TW_SMEM) return tw[i];
+        else return __ldg(&tw[i]);
+    }
+
     template <int s>
-    __device__ static __forceinline__ void stage(float4 (&reg)[8], float4* __restrict__ smem, const int tid,
+    __device__ static __forceinline__ void stage(C2 (&reg)[8], float4* __restrict__ smem, const int tid,
                                                  const int ln, const float2* __restrict__ tw, const int prior) {
         constexpr int Cs = 1 << (3 * s);
         constexpr int Ms = N / Cs;
@@ -113,12 +162,7 @@ struct LineFFT {
             radix8_inv(reg);
             if constexpr (Ms > 8) {
 #pragma unroll
-                for (int q = 1; q < 8; ++q) {
-                    const float2 w = __ldg(&tw[(s * 7 + q - 1) * T + tid]);
-                    const float4 r = reg[q];
-                    reg[q] = make_float4(r.x * w.x - r.y * w.y, r.x * w.y + r.y * w.x,
-                                         r.z * w.x - r.w * w.y, r.z * w.y + r.w * w.x);
-                }
+                for (int q = 1; q < 8; ++q) reg[q] = cmul(reg[q], twiddle(tw, (s * 7 + q - 1) * T + tid));
             }
             if constexpr (!last) {
                 constexpr int Mn = Ms / 8;
@@ -127,36 +171,35 @@ struct LineFFT {
                     if (prior + s > 0) __syncthreads();  // previous exchange fully read
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q) buf[phys<s>(tid + T * q, ln)] = reg[q];
+                for (int q = 0; q < 8; ++q) c2_store(&buf[phys<s>(tid + T * q, ln)], reg[q]);
                 __syncthreads();
                 constexpr int rn = (s + 1 == S - 1) ? RLAST : 8;
                 if constexpr (rn == 8) {
                     constexpr int Q = Mn / 8;  // threads per sub-problem in the next stage
                     const int cn = tid / Q, tn = tid & (Q - 1);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) reg[j] = buf[phys<s>((cn * 8 + j) * Q + tn, ln)];
+                    for (int j = 0; j < 8; ++j) reg[j] = c2_load(&buf[phys<s>((cn * 8 + j) * Q + tn, ln)]);
                 } else {
 #pragma unroll
                     for (int i = 0; i < 8 / rn; ++i)
 #pragma unroll
-                        for (int j = 0; j < rn; ++j) reg[i * rn + j] = buf[phys<s>((tid + T * i) * rn + j, ln)];
+                        for (int j = 0; j < rn; ++j) reg[i * rn + j] = c2_load(&buf[phys<s>((tid + T * i) * rn + j, ln)]);
                 }
             }
         } else if constexpr (RLAST == 4) {
             // two inverse DFT-4 on reg[0..3], reg[4..7]; output slot = i + 2*q
-            float4 o[8];
+            C2 o[8];
             radix4_inv(reg[0], reg[1], reg[2], reg[3], o[0], o[2], o[4], o[6]);
             radix4_inv(reg[4], reg[5], reg[6], reg[7], o[1], o[3], o[5], o[7]);
 #pragma unroll
             for (int j = 0; j < 8; ++j) reg[j] = o[j];
         } else {
             // RLAST == 2: four butterflies on (reg[2i], reg[2i+1]); output slot = i + 4*q
-            float4 o[8];
+            C2 o[8];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const float4 p = reg[2 * i], m = reg[2 * i + 1];
-                o[i] = make_float4(p.x + m.x, p.y + m.y, p.z + m.z, p.w + m.w);
-                o[i + 4] = make_float4(p.x - m.x, p.y - m.y, p.z - m.z, p.w - m.w);
+                o[i] = reg[2 * i] + reg[2 * i + 1];
+                o[i + 4] = reg[2 * i] - reg[2 * i + 1];
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) reg[j] = o[j];
@@ -167,7 +210,7 @@ struct LineFFT {
     // prior = number of exchanges this CTA has already performed (EXCHANGES per earlier transform).
     // Double buffer: exchange e uses buffer e & 1, one barrier each.  Single buffer: a leading
     // barrier protects the previous exchange's reads before the buffer is overwritten.
-    __device__ static __forceinline__ void run(float4 (&reg)[8], float4* __restrict__ smem, const int tid, const int ln,
+    __device__ static __forceinline__ void run(C2 (&reg)[8], float4* __restrict__ smem, const int tid, const int ln,
                                                const float2* __restrict__ tw, const int prior) {
         stage<0>(reg, smem, tid, ln, tw, prior);
         if constexpr (S > 1) stage<1>(reg, smem, tid, ln, tw, prior);

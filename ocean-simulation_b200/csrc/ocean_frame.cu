@@ -70,6 +70,29 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 #define OCEAN_COLS512_DB false
 #endif
 
+// Permute (FFT:73-78) + FillResultTextures (RF:16-34) on the packed pair layout.
+//   plane A: re = (Dx, Dy), im = (Dz, Dxz)      [DxDz = X + iZ, DyDxz = Y + i Z_x     TD:42-43]
+//   plane B: re = (Dyx, Dxx), im = (Dyz, Dzz)   [DyxDyz = Y_x + i Y_z, DxxDzz = X_x + i Z_z  TD:44-45]
+// sgn = (-1)^(x+y); lambda scales the horizontal displacement and its derivatives (1 = reference).
+struct Epilogue {
+    u64 aRe, aIm, b;
+    __device__ __forceinline__ Epilogue(float sgn, float lambda)
+        : aRe(pk2(sgn * lambda, sgn)), aIm(bc2(sgn * lambda)), b(pk2(sgn, sgn * lambda)) {}
+    // displacement = (Dx, Dy, Dz), alpha := 0  RF:25; also returns Dxz for the Jacobian
+    __device__ __forceinline__ float4 displacement(const C2& r, float& dxz) const {
+        const u64 re = mul2(r.re, aRe), im = mul2(r.im, aIm);
+        dxz = hi2(im);
+        return make_float4(lo2(re), hi2(re), lo2(im), 0.0f);
+    }
+    // derivatives = (Dyx, Dyz, Dxx, Dzz)  RF:26;  jac = (1 + Dxx)(1 + Dzz) - Dxz^2  RF:27
+    __device__ __forceinline__ float4 derivatives(const C2& r, float dxz, float& jac) const {
+        const u64 re = mul2(r.re, b), im = mul2(r.im, b);
+        const float dxx = hi2(re), dzz = hi2(im);
+        jac = (1.0f + dxx) * (1.0f + dzz) - dxz * dxz;
+        return make_float4(lo2(re), lo2(im), dxx, dzz);
+    }
+};
+
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
@@ -123,7 +146,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     const float time = a.time;
     cp_async_wait_all();
 
-    float4 pa[8], pb[8];
+    C2 pa[8], pb[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int x = tid + T * j;
@@ -146,9 +169,10 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
         const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
         const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
-        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz)
-        pa[j] = make_float4(X_x - Z_y, X_y + Z_x, hx - zdx_y, hy + zdx_x);
-        pb[j] = make_float4(ydx_x - ydz_y, ydx_y + ydz_x, xdx_x - zdz_y, xdx_y + zdz_x);
+        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz), each held as
+        // re = (re of first, re of second), im = (im of first, im of second)
+        pa[j] = C2{pk2(X_x - Z_y, hx - zdx_y), pk2(X_y + Z_x, hy + zdx_x)};
+        pb[j] = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
     }
 
     FFT::run(pa, smem, tid, row, a.twiddle, 0);
@@ -158,13 +182,13 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) out[tid + T * j] = pa[j];
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pa[j]);
     }
     FFT::run(pb, smem, tid, row, a.twiddle, FFT::EXCHANGES);
     if (active) {
         float4* __restrict__ out = a.rowsB + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) out[tid + T * j] = pb[j];
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
     }
 }
 
@@ -185,28 +209,24 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
     const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
 
-    float4 r[8];
+    const Epilogue ep(sgn, lambda);
+    C2 r[8];
     float dxz[8];
     {
         const float4* __restrict__ in = a.rowsA + base;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = __ldcg(in + (size_t)(tid + T * j) * N);
+        for (int j = 0; j < 8; ++j) r[j] = c2_from(__ldcg(in + (size_t)(tid + T * j) * N));
     }
     FFT::run(r, smem, tid, xw, a.twiddle, 0);
     {
         float4* __restrict__ disp = a.disp + base;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            // r = (DxDz, DyDxz) * sign;  displacement = (Dx, Dy, Dz)  RF:25 (alpha := 0)
-            const float dx = r[j].x * sgn, dz = r[j].y * sgn, dy = r[j].z * sgn;
-            dxz[j] = r[j].w * sgn * lambda;
-            st_stream(disp + (size_t)(tid + T * j) * N, make_float4(dx * lambda, dy, dz * lambda, 0.0f));
-        }
+        for (int j = 0; j < 8; ++j) st_stream(disp + (size_t)(tid + T * j) * N, ep.displacement(r[j], dxz[j]));
     }
     {
         const float4* __restrict__ in = a.rowsB + base;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = __ldcg(in + (size_t)(tid + T * j) * N);
+        for (int j = 0; j < 8; ++j) r[j] = c2_from(__ldcg(in + (size_t)(tid + T * j) * N));
     }
     FFT::run(r, smem, tid, xw, a.twiddle, FFT::EXCHANGES);
     {
@@ -217,12 +237,9 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const size_t o = (size_t)(tid + T * j) * N;
-            // r = (DyxDyz, DxxDzz) * sign;  derivatives RF:26
-            const float dyx = r[j].x * sgn, dyz = r[j].y * sgn;
-            const float dxx = r[j].z * sgn * lambda, dzz = r[j].w * sgn * lambda;
-            st_stream(deriv + o, make_float4(dyx, dyz, dxx, dzz));
-            // RF:27-32
-            const float jac = (1.0f + dxx) * (1.0f + dzz) - dxz[j] * dxz[j];
+            float jac;
+            st_stream(deriv + o, ep.derivatives(r[j], dxz[j], jac));
+            // RF:28-32
             float foam = zeroFoam ? 0.0f : ld_stream(turb + o).x;
             foam *= decay;
             if (foam < jac) foam += jac;
@@ -307,14 +324,14 @@ ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_con
         const int x = xt * W + xw;
         const size_t base = (size_t)layer * N * N + x;  // texel (x, 0) of this layer
         // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
-        const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
-        float4 r[8];
+        const Epilogue ep(((x + tid) & 1) ? -1.0f : 1.0f, lambda);
+        C2 r[8];
         float dxz[8], foam[8];
 
         // ---- pair A = (DxDz, DyDxz) -> displacement -------------------------------------------
         mbar_wait(&bars[0], parity);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = bufA[(tid + T * j) * W + xw];
+        for (int j = 0; j < 8; ++j) r[j] = c2_load(&bufA[(tid + T * j) * W + xw]);
         FFT::run(r, bufA, tid, xw, a.twiddle, 0);
         __syncthreads();  // every thread has finished reading bufA
         if (threadIdx.x == 0 && next < totalTiles) {
@@ -330,17 +347,12 @@ ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_con
         {
             float4* __restrict__ disp = a.disp + base;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                // r = (DxDz, DyDxz) * sign;  displacement = (Dx, Dy, Dz)  RF:25 (alpha := 0)
-                const float dx = r[j].x * sgn, dz = r[j].y * sgn, dy = r[j].z * sgn;
-                dxz[j] = r[j].w * sgn * lambda;
-                st_stream(disp + (size_t)(tid + T * j) * N, make_float4(dx * lambda, dy, dz * lambda, 0.0f));
-            }
+            for (int j = 0; j < 8; ++j) st_stream(disp + (size_t)(tid + T * j) * N, ep.displacement(r[j], dxz[j]));
         }
         // ---- pair B = (DyxDyz, DxxDzz) -> derivatives, Jacobian, foam --------------------------
         mbar_wait(&bars[1], parity);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = bufB[(tid + T * j) * W + xw];
+        for (int j = 0; j < 8; ++j) r[j] = c2_load(&bufB[(tid + T * j) * W + xw]);
         FFT::run(r, bufB, tid, xw, a.twiddle, 0);
         __syncthreads();
         if (threadIdx.x == 0 && next < totalTiles) {
@@ -353,10 +365,8 @@ ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_con
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const size_t o = (size_t)(tid + T * j) * N;
-                const float dyx = r[j].x * sgn, dyz = r[j].y * sgn;                      // RF:26
-                const float dxx = r[j].z * sgn * lambda, dzz = r[j].w * sgn * lambda;
-                st_stream(deriv + o, make_float4(dyx, dyz, dxx, dzz));
-                const float jac = (1.0f + dxx) * (1.0f + dzz) - dxz[j] * dxz[j];         // RF:27
+                float jac;
+                st_stream(deriv + o, ep.derivatives(r[j], dxz[j], jac));                 // RF:26-27
                 float f = foam[j] * decay;                                               // RF:28-30
                 if (f < jac) f += jac;                                                   // RF:31
                 st_stream(turb + o, make_float4(f, f, f, f));                            // RF:32

@@ -94,7 +94,8 @@ def test_row_pass_matches_oracle(pkg, po, N):
     rows = body.rowSpectra  # [2][C][N][N][4]
     for k in range(4):
         want = ob.get(po.ROWS0 + k)  # [C][N][N][2]
-        got = rows[k // 2][..., (k % 2) * 2:(k % 2) * 2 + 2]
+        # plane layout (re_first, re_second, im_first, im_second): ocean_fft.cuh packs two spectra SoA
+        got = np.stack([rows[k // 2][..., k % 2], rows[k // 2][..., 2 + k % 2]], axis=-1)
         assert rel_l2(got, want) <= TOL_FIELD_L2, "spectrum %d after the row pass" % k
     body.OnDisable()
 
