@@ -126,7 +126,9 @@ constexpr int ilog2(int n) { return n <= 1 ? 0 : 1 + ilog2(n >> 1); }
 // Twiddles: table tw[(s*7 + q-1)*T + tid] = e^{+2 pi i t q C_s / N}, t = tid mod (M_s/8), one entry
 // per (stage, q, thread) so that a warp reads 32 consecutive float2 (see make_twiddles, ocean_host.cu).
 // The table may live in global memory (read-only path) or in shared memory (persistent kernels).
-template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF, bool DENSE0 = false, bool TW_SMEM = false>
+// BAR_THREADS > 0: the CTA barrier is the named barrier 1 over the first BAR_THREADS threads (warp-
+// specialised kernels whose producer warp does not take part); 0 = __syncthreads().
+template <int N, int NL, bool INTERLEAVED, bool DOUBLE_BUF, bool DENSE0 = false, bool TW_SMEM = false, int BAR_THREADS = 0>
 struct LineFFT {
     static constexpr int T = N / 8;
     static constexpr int LOGN = ilog2(N);
@@ -147,6 +149,10 @@ struct LineFFT {
     }
     static constexpr int TWIDDLE_ENTRIES = (S - 1) * 7 * T;
 
+    __device__ static __forceinline__ void barrier() {
+        if constexpr (BAR_THREADS > 0) asm volatile("bar.sync 1, %0;" ::"n"(BAR_THREADS) : "memory");
+        else __syncthreads();
+    }
     __device__ static __forceinline__ float2 twiddle(const float2* __restrict__ tw, int i) {
         if constexpr (TW_SMEM) return tw[i];
         else return __ldg(&tw[i]);
@@ -168,11 +174,11 @@ struct LineFFT {
                 constexpr int Mn = Ms / 8;
                 float4* buf = smem + (DOUBLE_BUF ? ((prior + s) & 1) * BUF_ELEMS : 0);
                 if constexpr (!DOUBLE_BUF) {
-                    if (prior + s > 0) __syncthreads();  // previous exchange fully read
+                    if (prior + s > 0) barrier();  // previous exchange fully read
                 }
 #pragma unroll
                 for (int q = 0; q < 8; ++q) c2_store(&buf[phys<s>(tid + T * q, ln)], reg[q]);
-                __syncthreads();
+                barrier();
                 constexpr int rn = (s + 1 == S - 1) ? RLAST : 8;
                 if constexpr (rn == 8) {
                     constexpr int Q = Mn / 8;  // threads per sub-problem in the next stage

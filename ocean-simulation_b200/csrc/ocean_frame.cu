@@ -38,6 +38,10 @@ __device__ __forceinline__ void cp_async8(void* smemDst, const void* g) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(g) : "memory");
 }
+__device__ __forceinline__ void cp_async4(void* smemDst, const void* g) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(g) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
@@ -49,6 +53,31 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // reads-and-we-overwrite, so completion stays transitive along the stream.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Optional per-CTA phase trace (variants/ builds with -DOCEAN_TRACE only; never in the product build):
+// thread 0 of every CTA records %globaltimer / clock64 / %smid at phase boundaries.
+#ifdef OCEAN_TRACE
+#define OCEAN_TRACE_CTAS 8192
+#define OCEAN_TRACE_SLOTS 10
+__device__ unsigned long long g_trace[2][OCEAN_TRACE_CTAS][OCEAN_TRACE_SLOTS][2];
+__device__ unsigned g_trace_smid[2][OCEAN_TRACE_CTAS];
+__device__ __forceinline__ void trace_mark(int kernel, int cta, int slot) {
+    if (threadIdx.x == 0 && cta < OCEAN_TRACE_CTAS) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_trace[kernel][cta][slot][0] = t;
+        g_trace[kernel][cta][slot][1] = (unsigned long long)clock64();
+        if (slot == 0) {
+            unsigned sm;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+            g_trace_smid[kernel][cta] = sm;
+        }
+    }
+}
+#define TRACE(k, cta, slot) trace_mark(k, cta, slot)
+#else
+#define TRACE(k, cta, slot)
+#endif
 
 // tuning knobs for the headline size (overridable at build time for experiments)
 #ifndef OCEAN_ROWS512_R
@@ -130,6 +159,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     const float4* __restrict__ H = a.h0 + line * N;
     const float2* __restrict__ Wd = a.waveHot + line * N;
     pdl_trigger();
+    TRACE(0, blockIdx.x, 0);
 
     // Stage the whole row: 16 asynchronous copies per thread are in flight before any arithmetic.
     // Element x lands in the slot exchange 0 will later use for it, and thread `tid` only ever
@@ -145,6 +175,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     const float kz = (float)(y - N / 2) * dk;  // IS:111 (waveData.z)
     const float time = a.time;
     cp_async_wait_all();
+    TRACE(0, blockIdx.x, 1);
 
     C2 pa[8], pb[8];
 #pragma unroll
@@ -175,21 +206,27 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         pb[j] = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
     }
 
+    TRACE(0, blockIdx.x, 2);
     FFT::run(pa, smem, tid, row, a.twiddle, 0);
+    TRACE(0, blockIdx.x, 3);
     // h0 / waveHot are never written by a frame kernel, so everything above may overlap the previous
     // frame's column pass; the intermediate planes it is still reading may only be overwritten now.
     pdl_wait();
+    TRACE(0, blockIdx.x, 4);
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
 #pragma unroll
         for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pa[j]);
     }
+    TRACE(0, blockIdx.x, 5);
     FFT::run(pb, smem, tid, row, a.twiddle, FFT::EXCHANGES);
+    TRACE(0, blockIdx.x, 6);
     if (active) {
         float4* __restrict__ out = a.rowsB + line * N;
 #pragma unroll
         for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
     }
+    TRACE(0, blockIdx.x, 7);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -249,130 +286,176 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 }
 
 // ---------------------------------------------------------------------------------------------
-// Column pass, TMA version (N = 256, 512): persistent CTAs, one tile = W adjacent columns.
+// Column pass, TMA version (N = 256, 512): persistent, warp-specialised CTAs, two per SM.
 //
-//   * each of the two packed-spectra pairs of a tile is fetched by TMA tensor copies (boxes of
-//     4W floats x 256 rows) that land in natural [y][x] order in a shared-memory buffer;
-//   * that buffer IS exchange 0 of the FFT (DENSE0): thread (tid, xw) reads exactly the 8 points it
-//     later overwrites, so no barrier separates staging from the transform;
-//   * pair B, the turbulence texels and the next tile's pair A are in flight while pair A is
-//     transformed, so HBM/L2 latency is off the critical path after the first tile;
-//   * results leave through 128-bit streaming stores, W*16 contiguous bytes per row.
-#ifndef OCEAN_COLS512_TMA_W
-#define OCEAN_COLS512_TMA_W 8
+//   tile      = W adjacent columns x N rows of one layer, handled by W*N/8 compute threads;
+//   producer  = one extra warp whose lane 0 owns every bulk-asynchronous copy of the CTA:
+//                 TMA tensor loads of the two pair planes (boxes of 4W floats x 256 rows) that land
+//                 in natural [y][x] order in the buffer that IS exchange 0 of the FFT, and of the
+//                 incoming turbulence tile; TMA tensor stores of the three output tiles;
+//   compute   = wait full[A] -> transform in place -> stage the displacement texels in the same
+//               buffer -> fence.proxy.async + arrive on staged[A]; then the same for pair B, which
+//               stages derivatives in place and turbulence in a third buffer.
+// The compute warps never issue a global store and never wait for one: the producer stores the
+// staged tile, waits until the store has READ the buffer, and immediately refills it with the next
+// tile's plane, so loads, stores and butterflies of neighbouring tiles (and of the second CTA on the
+// SM) overlap instead of running in lockstep.  Twiddles live in shared memory.
+#ifndef OCEAN_COLS_TMA_W
+#define OCEAN_COLS_TMA_W 4
 #endif
-#ifndef OCEAN_COLS512_TMA_MINB
-#define OCEAN_COLS512_TMA_MINB 1
+#ifndef OCEAN_COLS_TMA_MINB
+#define OCEAN_COLS_TMA_MINB 2
 #endif
 
 template <int N> struct ColTmaCfg {
     static constexpr int T = N / 8;
-    static constexpr int W = (N == 512) ? OCEAN_COLS512_TMA_W : 8;
-    static constexpr int THREADS = W * T;
-    static constexpr int MINB = (N == 512) ? OCEAN_COLS512_TMA_MINB : 2;
+    static constexpr int W = OCEAN_COLS_TMA_W;
+    static constexpr int COMPUTE = W * T;                      // compute threads
+    static constexpr int THREADS = COMPUTE + 32;               // + producer warp
+    static constexpr int MINB = OCEAN_COLS_TMA_MINB;
     static constexpr int BOX_ROWS = N < 256 ? N : 256;
     static constexpr int NBOX = N / BOX_ROWS;
-    static constexpr int TILE_ELEMS = N * W;                    // float4 per pair-tile
-    static constexpr int SMEM_BYTES = 2 * TILE_ELEMS * 16 + 64; // two pair buffers + mbarriers
-    using FFT = LineFFT<N, W, true, false, true>;
+    static constexpr int TILE_ELEMS = N * W;                    // 128-bit elements per tile plane
+    using FFT = LineFFT<N, W, true, false, true, true, COMPUTE>;
+    static constexpr int TW_BYTES = FFT::TWIDDLE_ENTRIES * 8;
+    static constexpr int SMEM_BYTES = 3 * TILE_ELEMS * 16 + TW_BYTES + 64;  // A, B, turbulence staging, twiddles, mbarriers
 };
 
 template <int N>
 __global__ void __launch_bounds__(ColTmaCfg<N>::THREADS, ColTmaCfg<N>::MINB)
-ocean_cols_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const FrameArgs a,
-                      const int totalTiles) {
+ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs a, const int totalTiles) {
     using Cfg = ColTmaCfg<N>;
     using FFT = typename Cfg::FFT;
     constexpr int T = Cfg::T, W = Cfg::W, TILES_PER_LAYER = N / W;
     extern __shared__ __align__(128) float4 smem[];
     float4* bufA = smem;
     float4* bufB = smem + Cfg::TILE_ELEMS;
-    uint64_t* bars = (uint64_t*)(smem + 2 * Cfg::TILE_ELEMS);  // [0] pair A, [1] pair B
-    const int xw = threadIdx.x & (W - 1);
-    const int tid = threadIdx.x / W;
+    float4* bufT = smem + 2 * Cfg::TILE_ELEMS;
+    float2* twS = (float2*)(smem + 3 * Cfg::TILE_ELEMS);
+    uint64_t* bars = (uint64_t*)((char*)twS + Cfg::TW_BYTES);  // [0] full A, [1] full B, [2] staged A, [3] staged B
 
-    auto issue = [&](const CUtensorMap* map, float4* buf, uint64_t* bar, int tile) {
-        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
-        mbar_arrive_expect_tx(bar, Cfg::TILE_ELEMS * 16);
-#pragma unroll
-        for (int b = 0; b < Cfg::NBOX; ++b)
-            tma_load_2d(buf + b * Cfg::BOX_ROWS * W, map, bar, xt * W * 4, layer * N + b * Cfg::BOX_ROWS);
-    };
-
-    int tile = blockIdx.x;
     pdl_trigger();
+    TRACE(1, blockIdx.x, 0);
     if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], Cfg::COMPUTE);
+        mbar_init(&bars[3], Cfg::COMPUTE);
         mbar_fence_init();
     }
-    pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
-    if (threadIdx.x == 0) {
-        if (tile < totalTiles) {
-            issue(&mapA, bufA, &bars[0], tile);
-            issue(&mapB, bufB, &bars[1], tile);
-        }
-    }
+    // the twiddle table is immutable: copying it may overlap the previous kernel
+    for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twS[i] = __ldg(&a.twiddle[i]);
     __syncthreads();
+    pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
+    TRACE(1, blockIdx.x, 1);
 
+    // tile -> TMA coordinates: c0 = first fp32 of the tile's columns, c1 = first row
+    auto coords = [&](int tile, int& c0, int& c1) {
+        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
+        c0 = xt * W * 4;
+        c1 = layer * N;
+    };
+
+    if (threadIdx.x >= Cfg::COMPUTE) {
+        // ---------------- producer warp ----------------
+        if (threadIdx.x != Cfg::COMPUTE) return;
+        auto load = [&](const CUtensorMap* map, float4* buf, uint64_t* bar, int tile) {
+            int c0, c1;
+            coords(tile, c0, c1);
+#pragma unroll
+            for (int b = 0; b < Cfg::NBOX; ++b) tma_load_2d(buf + b * Cfg::BOX_ROWS * W, map, bar, c0, c1 + b * Cfg::BOX_ROWS);
+        };
+        // pair B travels with the tile's incoming turbulence texels (RF:28), which land in bufT
+        const bool needFoam = a.zeroFoam == 0;
+        auto loadB = [&](int tile) {
+            mbar_arrive_expect_tx(&bars[1], Cfg::TILE_ELEMS * 16 * (needFoam ? 2 : 1));
+            load(&maps.b, bufB, &bars[1], tile);
+            if (needFoam) load(&maps.turb, bufT, &bars[1], tile);
+        };
+        auto store = [&](const CUtensorMap* map, const float4* buf, int tile) {
+            int c0, c1;
+            coords(tile, c0, c1);
+#pragma unroll
+            for (int b = 0; b < Cfg::NBOX; ++b) tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, c0, c1 + b * Cfg::BOX_ROWS);
+        };
+        int tile = blockIdx.x;
+        if (tile < totalTiles) {
+            mbar_arrive_expect_tx(&bars[0], Cfg::TILE_ELEMS * 16);
+            load(&maps.a, bufA, &bars[0], tile);
+            loadB(tile);
+        }
+        uint32_t parity = 0;
+        for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
+            const int next = tile + gridDim.x;
+            mbar_wait(&bars[2], parity);  // displacement staged in bufA
+            store(&maps.disp, bufA, tile);
+            bulk_commit();
+            bulk_wait_read_all();
+            if (next < totalTiles) {
+                mbar_arrive_expect_tx(&bars[0], Cfg::TILE_ELEMS * 16);
+                load(&maps.a, bufA, &bars[0], next);
+            }
+            mbar_wait(&bars[3], parity);  // derivatives staged in bufB, turbulence in bufT
+            store(&maps.deriv, bufB, tile);
+            store(&maps.turb, bufT, tile);
+            bulk_commit();
+            bulk_wait_read_all();
+            if (next < totalTiles) loadB(next);
+        }
+        bulk_wait_all();
+        return;
+    }
+
+    // ---------------- compute warps ----------------
+    const int xw = threadIdx.x & (W - 1);
+    const int tid = threadIdx.x / W;
     const float lambda = a.lambda, decay = a.foamDecay;
     const bool zeroFoam = a.zeroFoam != 0;
     uint32_t parity = 0;
-    for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
-        const int next = tile + gridDim.x;
+    for (int tile = blockIdx.x; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
         const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
         const int x = xt * W + xw;
-        const size_t base = (size_t)layer * N * N + x;  // texel (x, 0) of this layer
         // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
         const Epilogue ep(((x + tid) & 1) ? -1.0f : 1.0f, lambda);
         C2 r[8];
-        float dxz[8], foam[8];
+        float dxz[8];
 
         // ---- pair A = (DxDz, DyDxz) -> displacement -------------------------------------------
         mbar_wait(&bars[0], parity);
+        TRACE(1, tile, 2);
 #pragma unroll
         for (int j = 0; j < 8; ++j) r[j] = c2_load(&bufA[(tid + T * j) * W + xw]);
-        FFT::run(r, bufA, tid, xw, a.twiddle, 0);
-        __syncthreads();  // every thread has finished reading bufA
-        if (threadIdx.x == 0 && next < totalTiles) {
-            fence_proxy_async();
-            issue(&mapA, bufA, &bars[0], next);
-        }
-        // turbulence of this tile: issued now, consumed after pair B's transform (RF:28)
-        {
-            const float4* __restrict__ turb = a.turb + base;
+        FFT::run(r, bufA, tid, xw, twS, 0);
+        FFT::barrier();  // every thread has finished reading the last exchange
+        TRACE(1, tile, 3);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) foam[j] = zeroFoam ? 0.0f : __ldcs(&turb[(size_t)(tid + T * j) * N].x);
-        }
-        {
-            float4* __restrict__ disp = a.disp + base;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) st_stream(disp + (size_t)(tid + T * j) * N, ep.displacement(r[j], dxz[j]));
-        }
+        for (int j = 0; j < 8; ++j) bufA[(tid + T * j) * W + xw] = ep.displacement(r[j], dxz[j]);
+        fence_proxy_async();
+        mbar_arrive(&bars[2]);
+        TRACE(1, tile, 4);
+
         // ---- pair B = (DyxDyz, DxxDzz) -> derivatives, Jacobian, foam --------------------------
         mbar_wait(&bars[1], parity);
+        TRACE(1, tile, 5);
 #pragma unroll
         for (int j = 0; j < 8; ++j) r[j] = c2_load(&bufB[(tid + T * j) * W + xw]);
-        FFT::run(r, bufB, tid, xw, a.twiddle, 0);
-        __syncthreads();
-        if (threadIdx.x == 0 && next < totalTiles) {
-            fence_proxy_async();
-            issue(&mapB, bufB, &bars[1], next);
-        }
-        {
-            float4* __restrict__ deriv = a.deriv + base;
-            float4* __restrict__ turb = a.turb + base;
+        FFT::run(r, bufB, tid, xw, twS, 0);
+        FFT::barrier();
+        TRACE(1, tile, 6);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const size_t o = (size_t)(tid + T * j) * N;
-                float jac;
-                st_stream(deriv + o, ep.derivatives(r[j], dxz[j], jac));                 // RF:26-27
-                float f = foam[j] * decay;                                               // RF:28-30
-                if (f < jac) f += jac;                                                   // RF:31
-                st_stream(turb + o, make_float4(f, f, f, f));                            // RF:32
-            }
+        for (int j = 0; j < 8; ++j) {
+            const int o = (tid + T * j) * W + xw;
+            float jac;
+            bufB[o] = ep.derivatives(r[j], dxz[j], jac);                             // RF:26-27
+            float f = zeroFoam ? 0.0f : bufT[o].x * decay;                           // RF:28-30 (incoming texel, TMA-staged)
+            if (f < jac) f += jac;                                                   // RF:31
+            bufT[o] = make_float4(f, f, f, f);                                       // RF:32
         }
+        fence_proxy_async();
+        mbar_arrive(&bars[3]);
+        TRACE(1, tile, 7);
     }
+    TRACE(1, blockIdx.x, 8);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -498,7 +581,7 @@ template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const Co
     }
     const int slots = num_sms() * ctasPerSM;
     const int grid = totalTiles < slots ? totalTiles : slots;
-    return launch_pdl(true, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m.a, m.b, a, totalTiles);
+    return launch_pdl(true, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
 }
 template <int N> static cudaError_t configure_tma() {
     cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
@@ -512,7 +595,8 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, ColsTmaMaps* out) {
+cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, float4* disp, float4* deriv, float4* turb,
+                           ColsTmaMaps* out) {
     out->valid = 0;
     if (!tma_size(N)) return cudaSuccess;
     static EncodeTiledFn encode = nullptr;
@@ -524,15 +608,15 @@ cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4*
         if (!fn || q != cudaDriverEntryPointSuccess) return cudaErrorNotSupported;
         encode = (EncodeTiledFn)fn;
     }
-    const int W = N == 512 ? ColTmaCfg<512>::W : ColTmaCfg<256>::W;
+    const int W = OCEAN_COLS_TMA_W;
     const int boxRows = N < 256 ? N : 256;
     const cuuint64_t dims[2] = {(cuuint64_t)N * 4, (cuuint64_t)layers * N};  // fp32 elements per row, rows
     const cuuint64_t strides[1] = {(cuuint64_t)N * 16};                      // bytes between rows
     const cuuint32_t box[2] = {(cuuint32_t)W * 4, (cuuint32_t)boxRows};
     const cuuint32_t estr[2] = {1, 1};
-    const float4* ptrs[2] = {rowsA, rowsB};
-    CUtensorMap* maps[2] = {&out->a, &out->b};
-    for (int i = 0; i < 2; ++i) {
+    const void* ptrs[5] = {rowsA, rowsB, disp, deriv, turb};
+    CUtensorMap* maps[5] = {&out->a, &out->b, &out->disp, &out->deriv, &out->turb};
+    for (int i = 0; i < 5; ++i) {
         CUresult r = encode(maps[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptrs[i], dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -558,7 +642,7 @@ template <int N> static const char* describe() {
         constexpr int M = (N == 512 || N == 256) ? N : 512;
         snprintf(buf, sizeof buf,
                  "rows<N=%d>: %d rows/CTA, %d threads, %d B smem (cp.async-staged row = exchange buffer); "
-                 "cols_tma<N=%d>: persistent, %d columns/tile, %d threads, %d B smem (TMA-staged tile = exchange buffer)",
+                 "cols_tma<N=%d>: persistent warp-specialised, %d columns/tile, %d threads, %d B smem (TMA in, TMA out)",
                  N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::SMEM_BYTES, N, ColTmaCfg<M>::W, ColTmaCfg<M>::THREADS,
                  ColTmaCfg<M>::SMEM_BYTES);
         return buf;
@@ -582,6 +666,15 @@ template <int N> static const char* describe() {
         case 2048: return CALL(2048);              \
         default: break;                            \
     }
+
+#ifdef OCEAN_TRACE
+extern "C" int ocean_debug_trace_copy(unsigned long long* times, unsigned* smids) {
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(times, g_trace, sizeof(g_trace)) != cudaSuccess) return 1;
+    if (cudaMemcpyFromSymbol(smids, g_trace_smid, sizeof(g_trace_smid)) != cudaSuccess) return 1;
+    return 0;
+}
+#endif
 
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early) {
 #define CALL(n) rows_launch<n>(a, s, early)

@@ -222,7 +222,7 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
         OCEAN_CUDA(launch_noise(seedDev, 1, N, noise, stream));
     }
     OCEAN_CUDA(configure_frame_kernels(N));
-    OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, &colsMaps));
+    OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
     for (int i = 0; i < RB; ++i) {
         OCEAN_CUDA(cudaMalloc(&rbStage[i], layerBytes4()));
         OCEAN_CUDA(cudaMallocHost(&rbHost[i], layerBytes4()));
@@ -414,7 +414,7 @@ int OceanEnsemble::create() {
         OCEAN_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
     }
     OCEAN_CUDA(configure_frame_kernels(N));
-    OCEAN_CUDA(make_cols_maps(N, batch * C, rowsA, rowsB, &colsMaps));
+    OCEAN_CUDA(make_cols_maps(N, batch * C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
     return OCEAN_OK;
 }
 

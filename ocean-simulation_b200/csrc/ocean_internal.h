@@ -69,15 +69,17 @@ struct FrameArgs {
     int zeroFoam;                      // 1: treat the incoming turbulence as zero (fresh texture)
 };
 
-// TMA descriptors of the two intermediate planes, viewed as 2-D fp32 tensors {4N, layers*N}; the
-// column kernel loads a tile of W adjacent columns (4W floats x up to 256 rows per box) with them.
+// TMA descriptors of the two intermediate planes and the three outputs, viewed as 2-D fp32 tensors
+// {4N, layers*N}; the column kernel moves tiles of W adjacent columns (4W floats x up to 256 rows per box).
 struct ColsTmaMaps {
-    CUtensorMap a, b;
+    CUtensorMap a, b;               // loads: the two intermediate planes
+    CUtensorMap disp, deriv, turb;  // stores: the three output arrays (same geometry)
     int valid = 0;
 };
 // Encodes the maps (driver entry point fetched through the runtime: no libcuda link).  Leaves
 // valid = 0 for sizes the TMA column kernel does not cover; those use the generic column kernel.
-cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, ColsTmaMaps* out);
+cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4* rowsB, float4* disp, float4* deriv, float4* turb,
+                           ColsTmaMaps* out);
 
 // launchers (return cudaGetLastError()); every launch bumps the launch counter
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
