@@ -226,6 +226,15 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
 #pragma unroll
         for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
     }
+    // publish: this CTA's rows of both planes are in memory (visible to the TMA loads of the column pass)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const size_t first = (size_t)blockIdx.x * R;  // R divides N: all rows of a CTA lie in one layer
+        const size_t n = first + R <= totalRows ? R : totalRows - first;
+        __threadfence();
+        fence_proxy_async_global();
+        atomicAdd(a.rowsDone + first / N, (unsigned long long)n);
+    }
     TRACE(0, blockIdx.x, 7);
 }
 
@@ -346,7 +355,10 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     // the twiddle table is immutable: copying it may overlap the previous kernel
     for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twS[i] = __ldg(&a.twiddle[i]);
     __syncthreads();
-    pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
+    // No griddepcontrol.wait here: the producer gates every tile on its layer's row counter instead.
+    // A counter can only reach the target after row CTAs of THIS frame passed their own
+    // griddepcontrol.wait, i.e. after everything earlier in the stream (the previous column pass
+    // included) has completed, so completion stays transitive along the stream.
     TRACE(1, blockIdx.x, 1);
 
     // tile -> TMA coordinates: c0 = first fp32 of the tile's columns, c1 = first row
@@ -378,8 +390,22 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 #pragma unroll
             for (int b = 0; b < Cfg::NBOX; ++b) tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, c0, c1 + b * Cfg::BOX_ROWS);
         };
+        int readyLayer = -1;  // layers are polled once: counters only grow
+        auto await_rows = [&](int tile) {
+            const int layer = tile / TILES_PER_LAYER;
+            if (layer == readyLayer) return;
+            const unsigned long long* flag = a.rowsDone + layer;
+            const long long t0 = clock64();
+            while (ld_acquire_gpu(flag) < a.rowsTarget) {
+                __nanosleep(64);
+                if (clock64() - t0 > (1ll << 33)) __trap();  // ~4 s: a lost row pass must not hang the GPU
+            }
+            fence_proxy_async_global();  // order the acquired generic-proxy writes before the TMA reads
+            readyLayer = layer;
+        };
         int tile = blockIdx.x;
         if (tile < totalTiles) {
+            await_rows(tile);
             mbar_arrive_expect_tx(&bars[0], Cfg::TILE_ELEMS * 16);
             load(&maps.a, bufA, &bars[0], tile);
             loadB(tile);
@@ -392,6 +418,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             bulk_commit();
             bulk_wait_read_all();
             if (next < totalTiles) {
+                await_rows(next);
                 mbar_arrive_expect_tx(&bars[0], Cfg::TILE_ELEMS * 16);
                 load(&maps.a, bufA, &bars[0], next);
             }
@@ -534,14 +561,30 @@ static bool pdl_enabled() {
     return v != 0;
 }
 template <class... KArgs, class... Args>
-static cudaError_t launch_pdl(bool early, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smemBytes, cudaStream_t s, Args&&... args) {
+static cudaError_t launch_pdl(bool early, const FrameArgs& fa, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smemBytes,
+                              cudaStream_t s, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smemBytes; cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (early && pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    if (fa.l2Window && fa.l2WindowBytes > 0 && fa.l2HitRatio > 0.0f) {
+        // keep the row -> column intermediate planes in the persisting part of L2: they are rewritten
+        // every frame and must never travel to HBM; everything else streams through the rest of L2
+        attr[n].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[n].val.accessPolicyWindow.base_ptr = const_cast<void*>(fa.l2Window);
+        attr[n].val.accessPolicyWindow.num_bytes = fa.l2WindowBytes;
+        attr[n].val.accessPolicyWindow.hitRatio = fa.l2HitRatio;
+        attr[n].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[n].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        ++n;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = (early && pdl_enabled()) ? 1 : 0;
+    cfg.numAttrs = n;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
     count_launch();
     return e;
@@ -551,12 +594,12 @@ template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t
     using Cfg = RowCfg<N>;
     const size_t totalRows = (size_t)a.layers * N;
     const unsigned grid = (unsigned)((totalRows + Cfg::R - 1) / Cfg::R);
-    return launch_pdl(early, ocean_rows_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, a);
+    return launch_pdl(early, a, ocean_rows_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, a);
 }
 template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t s) {
     using Cfg = ColCfg<N>;
     dim3 grid(N / Cfg::W, a.layers);
-    return launch_pdl(true, ocean_cols_kernel<N>, grid, dim3(Cfg::THREADS), Cfg::FFT::SMEM_BYTES, s, a);
+    return launch_pdl(true, a, ocean_cols_kernel<N>, grid, dim3(Cfg::THREADS), Cfg::FFT::SMEM_BYTES, s, a);
 }
 
 static int g_numSMs = 0;
@@ -581,7 +624,7 @@ template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const Co
     }
     const int slots = num_sms() * ctasPerSM;
     const int grid = totalTiles < slots ? totalTiles : slots;
-    return launch_pdl(true, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
+    return launch_pdl(true, a, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
 }
 template <int N> static cudaError_t configure_tma() {
     cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);

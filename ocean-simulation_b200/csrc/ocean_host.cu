@@ -15,7 +15,9 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -142,6 +144,83 @@ static std::vector<float2> make_twiddles(int N) {
     return tw;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Workspace: the two intermediate planes between the row and the column pass ([layers][N][N] float4
+// each, contiguous).  It is scratch: nothing in it survives a frame.  Handles that were put on the
+// same caller-provided stream (ocean_set_stream) are serialised by that stream, so they share one
+// workspace per (device, stream, size) -- like FFT plans sharing a work area -- and the planes stay
+// resident in L2 however many oceans rotate through them.  A handle on its own stream owns a
+// private workspace.
+struct Workspace {
+    int device = 0;
+    cudaStream_t stream = nullptr;  // nullptr: private
+    size_t planeBytes = 0;
+    float4* base = nullptr;
+    int refs = 0;
+    float4* planeA() const { return base; }
+    float4* planeB() const { return (float4*)((char*)base + planeBytes); }
+};
+static std::mutex g_wsMutex;
+static std::vector<Workspace*> g_workspaces;
+
+static Workspace* workspace_acquire(int device, cudaStream_t shared, size_t planeBytes) {
+    std::lock_guard<std::mutex> lock(g_wsMutex);
+    if (shared)
+        for (Workspace* w : g_workspaces)
+            if (w->device == device && w->stream == shared && w->planeBytes == planeBytes) { ++w->refs; return w; }
+    Workspace* w = new Workspace;
+    w->device = device; w->stream = shared; w->planeBytes = planeBytes; w->refs = 1;
+    if (cudaMalloc(&w->base, 2 * planeBytes) != cudaSuccess) { delete w; return nullptr; }
+    if (shared) g_workspaces.push_back(w);
+    return w;
+}
+static void workspace_release(Workspace* w) {
+    if (!w) return;
+    std::lock_guard<std::mutex> lock(g_wsMutex);
+    if (--w->refs > 0) return;
+    for (size_t i = 0; i < g_workspaces.size(); ++i)
+        if (g_workspaces[i] == w) { g_workspaces.erase(g_workspaces.begin() + i); break; }
+    cudaFree(w->base);
+    delete w;
+}
+
+// Optional persisting-L2 set-aside for the workspace, once per device: min(device maximum,
+// OCEAN_L2_PERSIST_MB MiB).  OFF by default (0): measured on B200 the per-launch access-policy window
+// made the frame slower (52 us vs 27.5 us at 4 x 512^2) -- sharing the workspace already keeps the
+// planes L2-resident.  Returns the bytes set aside (0 = disabled / unsupported).
+static size_t l2_set_aside(int device) {
+    static std::mutex m;
+    static std::vector<long long> cache(64, -1);
+    std::lock_guard<std::mutex> lock(m);
+    if (device < 0 || device >= (int)cache.size()) return 0;
+    if (cache[device] >= 0) return (size_t)cache[device];
+    long long want = 0;
+    if (const char* e = getenv("OCEAN_L2_PERSIST_MB")) want = atoll(e);
+    int maxPersist = 0, maxWindow = 0;
+    cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, device);
+    cudaDeviceGetAttribute(&maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, device);
+    long long bytes = want * (1ll << 20);
+    if (bytes > maxPersist) bytes = maxPersist;
+    if (bytes <= 0 || maxWindow <= 0 || cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)bytes) != cudaSuccess) {
+        cudaGetLastError();
+        bytes = 0;
+    }
+    cache[device] = bytes;
+    return (size_t)bytes;
+}
+static void l2_window(int device, const Workspace* w, FrameArgs* a) {
+    a->l2Window = nullptr; a->l2WindowBytes = 0; a->l2HitRatio = 0.0f;
+    const size_t aside = l2_set_aside(device);
+    if (!aside || !w) return;
+    int maxWindow = 0;
+    cudaDeviceGetAttribute(&maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, device);
+    size_t bytes = 2 * w->planeBytes;
+    if (bytes > (size_t)maxWindow) bytes = (size_t)maxWindow;
+    a->l2Window = w->base;
+    a->l2WindowBytes = bytes;
+    a->l2HitRatio = aside >= bytes ? 1.0f : (float)((double)aside / (double)bytes);
+}
+
 }  // namespace ocean
 
 using namespace ocean;
@@ -156,10 +235,15 @@ struct OceanHandle {
     cudaStream_t ownStream = nullptr, stream = nullptr, copyStream = nullptr;
     // arrays of WB:221-229 (+ noise WB:34); rowsA/rowsB replace the 4 spectra + ping-pong array
     float2* noise = nullptr;
-    float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr;
+    float4 *h0 = nullptr, *wave = nullptr;
+    Workspace* ws = nullptr;    // rowsA / rowsB point into it
+    FrameArgs l2{};             // only the l2Window* fields: computed once per workspace binding
+    float4 *rowsA = nullptr, *rowsB = nullptr;
     float4 *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     float2* waveHot = nullptr;  // (1/|k|, omega): compact copy of waveData read by the frame kernels
-    ColsTmaMaps colsMaps;       // TMA descriptors over rowsA / rowsB
+    ColsTmaMaps colsMaps;       // TMA descriptors over rowsA / rowsB and the outputs
+    unsigned long long* rowsDone = nullptr;  // per-layer row counters (row -> column hand-off)
+    uint64_t rowPasses = 0;                  // row passes issued so far: the counters' target is N * rowPasses
     float2* twiddle = nullptr;
     StateConsts* stateDev = nullptr;
     uint64_t* seedDev = nullptr;
@@ -190,8 +274,22 @@ struct OceanHandle {
     int Update(float time);
     void PollReadbacks(bool wait);
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
+    int AttachWorkspace(cudaStream_t shared);
     void OnDisable();
 };
+
+// (Re)binds the intermediate planes: a private workspace, or the one shared by every handle on `shared`.
+int OceanHandle::AttachWorkspace(cudaStream_t shared) {
+    Workspace* w = workspace_acquire(device, shared, C * texels() * sizeof(float4));
+    if (!w) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
+    workspace_release(ws);
+    ws = w;
+    rowsA = w->planeA();
+    rowsB = w->planeB();
+    l2_window(device, ws, &l2);
+    OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
+    return OCEAN_OK;
+}
 
 int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     const size_t t = texels();
@@ -202,8 +300,6 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&h0, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&wave, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&waveHot, C * t * sizeof(float2)));
-    OCEAN_CUDA(cudaMalloc(&rowsA, C * t * sizeof(float4)));
-    OCEAN_CUDA(cudaMalloc(&rowsB, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&disp, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&deriv, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&turb, C * t * sizeof(float4)));
@@ -211,6 +307,8 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&stateDev, sizeof(StateConsts)));
     OCEAN_CUDA(cudaMalloc(&seedDev, sizeof(uint64_t)));
+    OCEAN_CUDA(cudaMalloc(&rowsDone, C * sizeof(unsigned long long)));
+    OCEAN_CUDA(cudaMemsetAsync(rowsDone, 0, C * sizeof(unsigned long long), stream));
     OCEAN_CUDA(cudaMemsetAsync(disp, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(deriv, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(turb, 0, C * t * sizeof(float4), stream));  // fresh RenderTexture
@@ -222,7 +320,7 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
         OCEAN_CUDA(launch_noise(seedDev, 1, N, noise, stream));
     }
     OCEAN_CUDA(configure_frame_kernels(N));
-    OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
+    { int rc = AttachWorkspace(nullptr); if (rc != OCEAN_OK) return rc; }
     for (int i = 0; i < RB; ++i) {
         OCEAN_CUDA(cudaMalloc(&rbStage[i], layerBytes4()));
         OCEAN_CUDA(cudaMallocHost(&rbHost[i], layerBytes4()));
@@ -257,8 +355,17 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     a.time = time; a.lambda = params.lambda;
     a.foamDecay = expf(-2.0f);  // RF:29-30
     a.zeroFoam = foamZero ? 1 : 0;
-    if (which == 0 || which == 1) OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
+    a.rowsDone = rowsDone;
+    a.l2Window = l2.l2Window; a.l2WindowBytes = l2.l2WindowBytes; a.l2HitRatio = l2.l2HitRatio;
+    if (which == 0 || which == 1) {
+        if (rowPasses != (uint64_t)frame) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
+        ++rowPasses;
+        a.rowsTarget = (unsigned long long)N * rowPasses;
+        OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
+    }
     if (which == 0 || which == 2) {
+        if (rowPasses != (uint64_t)frame + 1) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
+        a.rowsTarget = (unsigned long long)N * rowPasses;
         OCEAN_CUDA(launch_cols(a, &colsMaps, stream));
         foamZero = false;
         ++frame;
@@ -355,7 +462,9 @@ int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* he
 void OceanHandle::OnDisable() {
     if (stream) cudaStreamSynchronize(stream);
     if (copyStream) cudaStreamSynchronize(copyStream);
-    void* dev[] = {noise, h0, wave, waveHot, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
+    workspace_release(ws);
+    ws = nullptr;
+    void* dev[] = {noise, h0, wave, waveHot, disp, deriv, turb, twiddle, stateDev, seedDev, rowsDone, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -375,8 +484,10 @@ struct OceanEnsemble {
     cudaStream_t stream = nullptr;
     float2* noise = nullptr;
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
+    Workspace* ws = nullptr;
     float2* waveHot = nullptr;
     ColsTmaMaps colsMaps;
+    unsigned long long* rowsDone = nullptr;  // per-layer row counters, zeroed before every wave
     float2* twiddle = nullptr;
     // double-buffered parameter / result staging so consecutive waves overlap
     StateConsts* stateDev[2] = {nullptr, nullptr};
@@ -398,9 +509,14 @@ int OceanEnsemble::create() {
     const size_t t = (size_t)N * N;
     OCEAN_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     OCEAN_CUDA(cudaMalloc(&noise, batch * t * sizeof(float2)));
-    float4** arrs[] = {&h0, &wave, &rowsA, &rowsB, &disp, &deriv, &turb};
+    float4** arrs[] = {&h0, &wave, &disp, &deriv, &turb};
     for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
+    ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4));
+    if (!ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
+    rowsA = ws->planeA();
+    rowsB = ws->planeB();
     OCEAN_CUDA(cudaMalloc(&waveHot, (size_t)batch * C * t * sizeof(float2)));
+    OCEAN_CUDA(cudaMalloc(&rowsDone, (size_t)batch * C * sizeof(unsigned long long)));
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
@@ -461,6 +577,10 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
+        fa.rowsDone = rowsDone;
+        fa.rowsTarget = (unsigned long long)N;
+        l2_window(device, ws, &fa);
+        OCEAN_CUDA(cudaMemsetAsync(rowsDone, 0, (size_t)nb * C * sizeof(unsigned long long), stream));
         OCEAN_CUDA(launch_rows(fa, stream, false));  // follows the init kernel: no early start
         OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
         OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
@@ -479,7 +599,9 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
 
 void OceanEnsemble::destroy() {
     if (stream) cudaStreamSynchronize(stream);
-    void* dev[] = {noise, h0, wave, waveHot, rowsA, rowsB, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
+    workspace_release(ws);
+    ws = nullptr;
+    void* dev[] = {noise, h0, wave, waveHot, disp, deriv, turb, twiddle, rowsDone, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) {
@@ -666,6 +788,8 @@ int ocean_reset_foam(OceanHandle* h) {
     OCEAN_CUDA(cudaMemsetAsync(h->turb, 0, h->C * h->layerBytes4(), h->stream));
     h->foamZero = true;
     h->frame = 0;
+    h->rowPasses = 0;
+    OCEAN_CUDA(cudaMemsetAsync(h->rowsDone, 0, h->C * sizeof(unsigned long long), h->stream));
     return OCEAN_OK;
 }
 
@@ -691,7 +815,7 @@ int ocean_set_stream(OceanHandle* h, void* s) {
     DeviceScope scope(h->device);
     OCEAN_CUDA(cudaStreamSynchronize(h->stream));
     h->stream = s ? (cudaStream_t)s : h->ownStream;
-    return OCEAN_OK;
+    return h->AttachWorkspace(s ? (cudaStream_t)s : nullptr);
 }
 
 int ocean_describe(OceanHandle* h, char* buf, size_t bufBytes) {

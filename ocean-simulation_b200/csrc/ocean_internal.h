@@ -67,6 +67,16 @@ struct FrameArgs {
     float lambda;
     float foamDecay;                   // exp(-2.0f)  RF:29-30
     int zeroFoam;                      // 1: treat the incoming turbulence as zero (fresh texture)
+    // Row -> column hand-off per layer: every row CTA adds the rows it finished to rowsDone[layer]
+    // (release); the TMA column kernel starts a tile of `layer` once rowsDone[layer] >= rowsTarget
+    // (acquire), so columns of the first layers overlap the row pass of the last ones.
+    unsigned long long* rowsDone;      // device, one counter per layer
+    unsigned long long rowsTarget;     // N * (row passes issued on these counters so far)
+    // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
+    // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
+    const void* l2Window;
+    size_t l2WindowBytes;
+    float l2HitRatio;
 };
 
 // TMA descriptors of the two intermediate planes and the three outputs, viewed as 2-D fp32 tensors
