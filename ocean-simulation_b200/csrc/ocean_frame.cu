@@ -49,8 +49,11 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
 // attribute may begin while its predecessor in the stream is still running.  pdl_trigger() lets the
 // successor start early; pdl_wait() blocks until every predecessor grid has completed and flushed.
-// Both kernels of a frame call pdl_wait() before touching anything a predecessor kernel writes or
-// reads-and-we-overwrite, so completion stays transitive along the stream.
+// The frame kernels do not use pdl_wait() for their mutual dependencies: those are per-layer
+// release/acquire counters (FrameArgs::rowsDone / colsDone), which let the row pass of frame f+1 run
+// next to the column pass of frame f on the same SMs.  Completion stays transitive along the stream
+// through the counters: a column tile waits for its layer's rows, and a row CTA waits, before its first
+// store, for the previous frame's columns of its layer to be finished and stored.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
@@ -210,8 +213,10 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     FFT::run(pa, smem, tid, row, a.twiddle, 0);
     TRACE(0, blockIdx.x, 3);
     // h0 / waveHot are never written by a frame kernel, so everything above may overlap the previous
-    // frame's column pass; the intermediate planes it is still reading may only be overwritten now.
-    pdl_wait();
+    // frame's column pass; the workspace rows it may still be reading can only be overwritten once it
+    // has finished this layer.
+    if (threadIdx.x == 0) spin_until_ge(a.colsDone + (size_t)blockIdx.x * R / N, a.colsTarget);
+    __syncthreads();
     TRACE(0, blockIdx.x, 4);
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
@@ -234,6 +239,188 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         __threadfence();
         fence_proxy_async_global();
         atomicAdd(a.rowsDone + first / N, (unsigned long long)n);
+    }
+    TRACE(0, blockIdx.x, 7);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row pass for N >= 256: one CTA = the two rows y and N-y of one layer (the pair (0, N/2) for the
+// two self-mirrored rows), 2 * N/8 threads.
+//
+// h(k,t) = h0(k) e^{i w t} + conj(h0(-k)) e^{-i w t}  (TD:26) satisfies h(-k,t) = conj h(k,t): the
+// reference stores conj h0(-k) next to h0(k) and evaluates every texel; here a CTA owns a texel
+// AND its mirror ((N-x)%N, (N-y)%N), so it
+//   * reads the compact h0(k) once per texel (8 B instead of the 16 B packing) and (1/|k|, w)
+//     only for the half of the texels it evaluates  ->  12 B instead of 24 B per texel-cascade;
+//   * evaluates sincos and h for half of the texels and hands conj h to the mirror through
+//     shared memory;
+//   * builds the eight derived spectra (TD:29-45) directly in the packed pair layout with f32x2
+//     arithmetic: every component is hx * (c0, c1) + hy * (c2, c3) with k-only coefficients.
+// Staging, the h exchange and the FFT exchanges share one shared-memory buffer; twiddles are
+// staged in shared memory by cp.async alongside the row data.
+#ifndef OCEAN_ROWPAIR_MINB
+#define OCEAN_ROWPAIR_MINB 7
+#endif
+template <int N> struct RowPairCfg {
+    static constexpr int T = N / 8;
+    static constexpr int THREADS = 2 * T;
+    static constexpr int MINB = (N == 512) ? OCEAN_ROWPAIR_MINB : 1;
+    using FFT = LineFFT<N, 2, false, false, false, true>;
+    static constexpr int TW_BYTES = FFT::TWIDDLE_ENTRIES * 8;
+    static constexpr int SMEM_BYTES = 2 * N * 16 + TW_BYTES;
+};
+
+// sin and cos of a phase: 3-term Cody-Waite reduction to [-pi/4, pi/4] (the constants CUDA's own
+// sincosf uses on its fast path, valid below 105615 rad) followed by the SFU approximations, whose
+// absolute error (~4e-7) is of the order of the transform's own rounding.  Larger phases take the
+// library path.
+__device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
+    if (fabsf(x) > 105615.0f) {
+        sincosf(x, &sn, &cs);
+        return;
+    }
+    const float magic = 12582912.0f;  // 1.5 * 2^23: adding it rounds to the nearest integer
+    const float qf = __fmaf_rn(x, 0.636619772f, magic);
+    const int iq = __float_as_int(qf);  // low bits = round(x * 2/pi)
+    const float q = qf - magic;
+    float r = __fmaf_rn(q, -1.57079601e+00f, x);
+    r = __fmaf_rn(q, -3.13916473e-07f, r);
+    r = __fmaf_rn(q, -5.39030253e-15f, r);
+    const float s0 = __sinf(r), c0 = __cosf(r);
+    const bool odd = iq & 1;
+    const float sv = odd ? c0 : s0, cv = odd ? s0 : c0;
+    sn = __int_as_float(__float_as_int(sv) ^ ((iq & 2) << 30));
+    cs = __int_as_float(__float_as_int(cv) ^ (((iq + 1) & 2) << 30));
+}
+
+template <int N>
+__global__ void __launch_bounds__(RowPairCfg<N>::THREADS, RowPairCfg<N>::MINB) ocean_rows_pair_kernel(const FrameArgs a) {
+    using Cfg = RowPairCfg<N>;
+    using FFT = typename Cfg::FFT;
+    constexpr int T = Cfg::T, HALF = N / 2;
+    extern __shared__ float4 smem[];
+    float4* X = smem;                         // [2][N]: staging, then h hand-over, then the FFT exchanges
+    float2* twS = (float2*)(smem + 2 * N);
+    const int r = threadIdx.x / T, tid = threadIdx.x - r * T;
+    const int layer = blockIdx.x / HALF, p = blockIdx.x - layer * HALF;
+    // pair p >= 1: rows (p, N-p), each the mirror of the other; pair 0: rows 0 and N/2, self-mirrored
+    const int y = p == 0 ? (r ? HALF : 0) : (r ? N - p : p);
+    const int ym = (N - y) & (N - 1);
+    const int rm = p == 0 ? r : 1 - r;        // buffer slot of the mirror row
+    float4* Xr = X + r * N;
+    const float4* Xm = X + rm * N;
+    const size_t rowBase = ((size_t)layer * N + y) * N, mirBase = ((size_t)layer * N + ym) * N;
+    pdl_trigger();
+    TRACE(0, blockIdx.x, 0);
+
+    // ---- stage (all private to this thread: no barrier) ----------------------------------------
+    // evaluated texels: x = tid + T*j, j < 4 (thread 0 also takes x = N/2, its own mirror column)
+    //   slot(x_j).xy = h0(x_j, y), .zw = (1/|k|, w);  slot(x_{j+4}).xy = h0 of the mirror texel
+    // thread 0, j = 4: h0 -> slot(x_5).zw, (1/|k|, w) -> slot(x_6).zw, mirror h0 -> slot(x_7).zw
+    for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES / 2; i += Cfg::THREADS) cp_async16((float4*)twS + i, (const float4*)a.twiddle + i);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int x = tid + T * j, mx = (N - x) & (N - 1);
+        cp_async8(&Xr[x].x, a.h0c + rowBase + x);
+        cp_async8(&Xr[x].z, a.waveHot + rowBase + x);
+        cp_async8(&Xr[x + 4 * T].x, a.h0c + mirBase + mx);
+    }
+    if (tid == 0) {
+        cp_async8(&Xr[5 * T].z, a.h0c + rowBase + HALF);
+        cp_async8(&Xr[6 * T].z, a.waveHot + rowBase + HALF);
+        cp_async8(&Xr[7 * T].z, a.h0c + mirBase + HALF);
+    }
+    const float dk = a.dk[layer % a.C];
+    const float kz = (float)(y - HALF) * dk;  // IS:111 (waveData.z)
+    const float time = a.time;
+    cp_async_wait_all();
+    TRACE(0, blockIdx.x, 1);
+
+    // ---- h(k,t) at the evaluated texels (TD:23-26) ------------------------------------------------
+    float hx[8], hy[8], ik[8];
+    auto evolve = [&](float2 h0, float2 hm, float2 wv, float& ox, float& oy) {
+        float sn, cs;
+        phase_sincos(wv.y * time, sn, cs);
+        // h0 * e + conj(h0(-k)) * conj(e),  conj(h0(-k)) = (hm.x, -hm.y)
+        ox = (h0.x * cs - h0.y * sn) + (hm.x * cs - hm.y * sn);
+        oy = (h0.x * sn + h0.y * cs) - (hm.y * cs + hm.x * sn);
+    };
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float4 own = Xr[tid + T * j];
+        const float4 mir = Xr[tid + T * (j + 4)];
+        evolve(make_float2(own.x, own.y), make_float2(mir.x, mir.y), make_float2(own.z, own.w), hx[j], hy[j]);
+        ik[j] = own.z;
+    }
+    if (tid == 0) {
+        const float4 s5 = Xr[5 * T], s6 = Xr[6 * T], s7 = Xr[7 * T];
+        evolve(make_float2(s5.z, s5.w), make_float2(s7.z, s7.w), make_float2(s6.z, s6.w), hx[4], hy[4]);
+        ik[4] = s6.z;
+    }
+    // ---- hand conj h to the mirror texels -----------------------------------------------------------
+    // (every slot written below was staged for, and has been read by, this thread only)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) Xr[tid + T * j] = make_float4(hx[j], hy[j], ik[j], 0.0f);
+    if (tid == 0) Xr[4 * T] = make_float4(hx[4], hy[4], ik[4], 0.0f);
+    __syncthreads();
+#pragma unroll
+    for (int j = 4; j < 8; ++j) {
+        if (j == 4 && tid == 0) continue;  // x = N/2 was evaluated above
+        const int x = tid + T * j;
+        const float4 v = Xm[(N - x) & (N - 1)];
+        hx[j] = v.x;
+        hy[j] = -v.y;
+        ik[j] = v.z;
+    }
+    TRACE(0, blockIdx.x, 2);
+
+    // ---- derived spectra, packed: component = hx * (c0, c1) + hy * (c2, c3)  (TD:29-45) -------------
+    //   DxDz   = X + iZ     = ih kx/|k| - h kz/|k|      DyDxz  = Y + i Z_x = h - i h kx kz/|k|
+    //   DyxDyz = Y_x + iY_z = ih kx - h kz              DxxDzz = X_x + iZ_z = -h kx^2/|k| - i h kz^2/|k|
+    C2 v[8];
+    auto plane_a = [&](int j) {
+        const float kx = (float)(tid + T * j - HALF) * dk;  // IS:111 (waveData.x)
+        const float ca = kx * ik[j], cb = kz * ik[j], cc = ca * kz;
+        const u64 H = bc2(hx[j]), G = bc2(hy[j]);
+        v[j] = C2{fma2(H, pk2(-cb, 1.0f), mul2(G, pk2(-ca, cc))), fma2(H, pk2(ca, -cc), mul2(G, pk2(-cb, 1.0f)))};
+    };
+    auto plane_b = [&](int j) {
+        const float kx = (float)(tid + T * j - HALF) * dk;
+        const float ca = kx * ik[j], cb = kz * ik[j], cd = ca * kx, ce = cb * kz;
+        const u64 H = bc2(hx[j]), G = bc2(hy[j]);
+        v[j] = C2{fma2(H, pk2(-kz, -cd), mul2(G, pk2(-kx, ce))), fma2(H, pk2(kx, -ce), mul2(G, pk2(-kz, -cd)))};
+    };
+#pragma unroll
+    for (int j = 0; j < 8; ++j) plane_a(j);
+    FFT::run(v, X, tid, r, twS, 1);  // prior = 1: barrier before the first exchange (the hand-over reads)
+    TRACE(0, blockIdx.x, 3);
+    // h0c / waveHot are never written by a frame kernel, so everything above may overlap the previous
+    // frame's column pass; the workspace rows it may still be reading can only be overwritten once it
+    // has finished this layer.
+    if (threadIdx.x == 0) spin_until_ge(a.colsDone + layer, a.colsTarget);
+    __syncthreads();
+    TRACE(0, blockIdx.x, 4);
+    {
+        float4* __restrict__ out = a.rowsA + rowBase;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], v[j]);
+    }
+    TRACE(0, blockIdx.x, 5);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) plane_b(j);
+    FFT::run(v, X, tid, r, twS, 1 + FFT::EXCHANGES);
+    TRACE(0, blockIdx.x, 6);
+    {
+        float4* __restrict__ out = a.rowsB + rowBase;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], v[j]);
+    }
+    // publish: both rows of both planes are in memory (visible to the TMA loads of the column pass)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        fence_proxy_async_global();
+        atomicAdd(a.rowsDone + layer, 2ull);
     }
     TRACE(0, blockIdx.x, 7);
 }
@@ -292,6 +479,12 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
             st_stream(turb + o, make_float4(foam, foam, foam, foam));
         }
     }
+    // hand the layer's workspace rows back to the next frame's row pass
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(a.colsDone + blockIdx.y, (unsigned long long)W);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -314,6 +507,11 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 #endif
 #ifndef OCEAN_COLS_TMA_MINB
 #define OCEAN_COLS_TMA_MINB 2
+#endif
+// persistent grid = SMs x this many CTAs (capped by occupancy).  Fewer column CTAs per SM leave room
+// for row CTAs of the NEXT frame to run in the shadow of this (HBM-bound) kernel.
+#ifndef OCEAN_COLS_TMA_CTAS_PER_SM
+#define OCEAN_COLS_TMA_CTAS_PER_SM 2
 #endif
 
 template <int N> struct ColTmaCfg {
@@ -394,12 +592,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         auto await_rows = [&](int tile) {
             const int layer = tile / TILES_PER_LAYER;
             if (layer == readyLayer) return;
-            const unsigned long long* flag = a.rowsDone + layer;
-            const long long t0 = clock64();
-            while (ld_acquire_gpu(flag) < a.rowsTarget) {
-                __nanosleep(64);
-                if (clock64() - t0 > (1ll << 33)) __trap();  // ~4 s: a lost row pass must not hang the GPU
-            }
+            spin_until_ge(a.rowsDone + layer, a.rowsTarget);
             fence_proxy_async_global();  // order the acquired generic-proxy writes before the TMA reads
             readyLayer = layer;
         };
@@ -428,8 +621,13 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             bulk_commit();
             bulk_wait_read_all();
             if (next < totalTiles) loadB(next);
+            // the tile's three outputs are in memory: hand its columns back (the next frame's row pass
+            // may overwrite the workspace; the next frame's column pass may read this turbulence)
+            bulk_wait_all();
+            fence_proxy_async_global();
+            __threadfence();
+            atomicAdd(a.colsDone + tile / TILES_PER_LAYER, (unsigned long long)W);
         }
-        bulk_wait_all();
         return;
     }
 
@@ -596,6 +794,16 @@ template <int N> static cudaError_t rows_launch(const FrameArgs& a, cudaStream_t
     const unsigned grid = (unsigned)((totalRows + Cfg::R - 1) / Cfg::R);
     return launch_pdl(early, a, ocean_rows_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, a);
 }
+template <int N> static cudaError_t rows_pair_launch(const FrameArgs& a, cudaStream_t s, bool early) {
+    using Cfg = RowPairCfg<N>;
+    return launch_pdl(early, a, ocean_rows_pair_kernel<N>, dim3((unsigned)(a.layers * (N / 2))), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, a);
+}
+template <int N> static cudaError_t configure_pair() {
+    cudaError_t e = cudaFuncSetAttribute(ocean_rows_pair_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, RowPairCfg<N>::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    cudaFuncSetAttribute(ocean_rows_pair_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaSuccess;
+}
 template <int N> static cudaError_t cols_launch(const FrameArgs& a, cudaStream_t s) {
     using Cfg = ColCfg<N>;
     dim3 grid(N / Cfg::W, a.layers);
@@ -621,6 +829,7 @@ template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const Co
         int n = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_cols_tma_kernel<N>, Cfg::THREADS, Cfg::SMEM_BYTES);
         ctasPerSM = n > 0 ? n : 1;
+        if (ctasPerSM > OCEAN_COLS_TMA_CTAS_PER_SM) ctasPerSM = OCEAN_COLS_TMA_CTAS_PER_SM;
     }
     const int slots = num_sms() * ctasPerSM;
     const int grid = totalTiles < slots ? totalTiles : slots;
@@ -720,6 +929,20 @@ extern "C" int ocean_debug_trace_copy(unsigned long long* times, unsigned* smids
 #endif
 
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early) {
+    // The pair-row kernel moves half the bytes and issues fewer instructions, but on B200 at N = 512 the
+    // one-row kernel is still ~1 us/frame faster (more, smaller CTAs hide more latency): it stays the
+    // default until the pair kernel wins.  OCEAN_ROWS_PAIR=1 (or -DOCEAN_ROWS_USE_PAIR) selects it.
+#ifdef OCEAN_ROWS_USE_PAIR
+    const bool legacy = false;
+#else
+    static const bool legacy = getenv("OCEAN_ROWS_PAIR") == nullptr;
+#endif
+    if (!legacy) {
+        if (a.N == 256) return rows_pair_launch<256>(a, s, early);
+        if (a.N == 512) return rows_pair_launch<512>(a, s, early);
+        if (a.N == 1024) return rows_pair_launch<1024>(a, s, early);
+        if (a.N == 2048) return rows_pair_launch<2048>(a, s, early);
+    }
 #define CALL(n) rows_launch<n>(a, s, early)
     OCEAN_DISPATCH_N(a.N, CALL)
 #undef CALL
@@ -736,6 +959,10 @@ cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_
     return cudaErrorInvalidValue;
 }
 cudaError_t configure_frame_kernels(int N) {
+    if (N == 256) { cudaError_t e = configure_pair<256>(); if (e != cudaSuccess) return e; }
+    if (N == 512) { cudaError_t e = configure_pair<512>(); if (e != cudaSuccess) return e; }
+    if (N == 1024) { cudaError_t e = configure_pair<1024>(); if (e != cudaSuccess) return e; }
+    if (N == 2048) { cudaError_t e = configure_pair<2048>(); if (e != cudaSuccess) return e; }
     if (N == 512) { cudaError_t e = configure_tma<512>(); if (e != cudaSuccess) return e; }
     if (N == 256) { cudaError_t e = configure_tma<256>(); if (e != cudaSuccess) return e; }
 #define CALL(n) configure<n>()

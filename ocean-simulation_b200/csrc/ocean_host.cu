@@ -157,20 +157,34 @@ struct Workspace {
     size_t planeBytes = 0;
     float4* base = nullptr;
     int refs = 0;
+    // Hand-off counters live with the memory they guard.  counters[0..layers) = rows written into the
+    // planes (row -> column), counters[layers..2*layers) = columns consumed and stored (column -> row).
+    // rowPasses / colPasses count the passes ENQUEUED on this workspace (its users are serialised by
+    // one stream, so enqueue order is execution order); a pass's target is N * its ordinal.
+    int layers = 0;
+    unsigned long long* counters = nullptr;
+    uint64_t rowPasses = 0, colPasses = 0;
     float4* planeA() const { return base; }
     float4* planeB() const { return (float4*)((char*)base + planeBytes); }
 };
 static std::mutex g_wsMutex;
 static std::vector<Workspace*> g_workspaces;
 
-static Workspace* workspace_acquire(int device, cudaStream_t shared, size_t planeBytes) {
+static Workspace* workspace_acquire(int device, cudaStream_t shared, size_t planeBytes, int layers) {
     std::lock_guard<std::mutex> lock(g_wsMutex);
     if (shared)
         for (Workspace* w : g_workspaces)
             if (w->device == device && w->stream == shared && w->planeBytes == planeBytes) { ++w->refs; return w; }
     Workspace* w = new Workspace;
     w->device = device; w->stream = shared; w->planeBytes = planeBytes; w->refs = 1;
+    w->layers = layers;
     if (cudaMalloc(&w->base, 2 * planeBytes) != cudaSuccess) { delete w; return nullptr; }
+    if (cudaMalloc(&w->counters, 2 * layers * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(w->counters, 0, 2 * layers * sizeof(unsigned long long)) != cudaSuccess) {
+        cudaFree(w->base);
+        delete w;
+        return nullptr;
+    }
     if (shared) g_workspaces.push_back(w);
     return w;
 }
@@ -181,7 +195,17 @@ static void workspace_release(Workspace* w) {
     for (size_t i = 0; i < g_workspaces.size(); ++i)
         if (g_workspaces[i] == w) { g_workspaces.erase(g_workspaces.begin() + i); break; }
     cudaFree(w->base);
+    cudaFree(w->counters);
     delete w;
+}
+// Stamps a frame's hand-off targets.  rows / cols say which passes this launch sequence contains.
+static void workspace_stamp(Workspace* w, int N, bool rows, bool cols, FrameArgs* a) {
+    if (rows) ++w->rowPasses;
+    a->rowsDone = w->counters;
+    a->colsDone = w->counters + w->layers;
+    a->rowsTarget = (unsigned long long)N * w->rowPasses;  // the column pass waits for this frame's rows
+    a->colsTarget = (unsigned long long)N * w->colPasses;  // the row pass waits for every earlier column pass
+    if (cols) ++w->colPasses;
 }
 
 // Optional persisting-L2 set-aside for the workspace, once per device: min(device maximum,
@@ -241,9 +265,9 @@ struct OceanHandle {
     float4 *rowsA = nullptr, *rowsB = nullptr;
     float4 *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     float2* waveHot = nullptr;  // (1/|k|, omega): compact copy of waveData read by the frame kernels
+    float2* h0c = nullptr;      // h0(k): compact copy of h0.xy read by the pair-row kernel
     ColsTmaMaps colsMaps;       // TMA descriptors over rowsA / rowsB and the outputs
-    unsigned long long* rowsDone = nullptr;  // per-layer row counters (row -> column hand-off)
-    uint64_t rowPasses = 0;                  // row passes issued so far: the counters' target is N * rowPasses
+    bool rowsPending = false;   // ocean_step_partial: a row pass was issued and its column pass has not been
     float2* twiddle = nullptr;
     StateConsts* stateDev = nullptr;
     uint64_t* seedDev = nullptr;
@@ -280,7 +304,7 @@ struct OceanHandle {
 
 // (Re)binds the intermediate planes: a private workspace, or the one shared by every handle on `shared`.
 int OceanHandle::AttachWorkspace(cudaStream_t shared) {
-    Workspace* w = workspace_acquire(device, shared, C * texels() * sizeof(float4));
+    Workspace* w = workspace_acquire(device, shared, C * texels() * sizeof(float4), C);
     if (!w) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
     workspace_release(ws);
     ws = w;
@@ -300,6 +324,7 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&h0, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&wave, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&waveHot, C * t * sizeof(float2)));
+    OCEAN_CUDA(cudaMalloc(&h0c, C * t * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&disp, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&deriv, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&turb, C * t * sizeof(float4)));
@@ -307,8 +332,6 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&stateDev, sizeof(StateConsts)));
     OCEAN_CUDA(cudaMalloc(&seedDev, sizeof(uint64_t)));
-    OCEAN_CUDA(cudaMalloc(&rowsDone, C * sizeof(unsigned long long)));
-    OCEAN_CUDA(cudaMemsetAsync(rowsDone, 0, C * sizeof(unsigned long long), stream));
     OCEAN_CUDA(cudaMemsetAsync(disp, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(deriv, 0, C * t * sizeof(float4), stream));
     OCEAN_CUDA(cudaMemsetAsync(turb, 0, C * t * sizeof(float4), stream));  // fresh RenderTexture
@@ -338,7 +361,7 @@ int OceanHandle::CalculateInitialSpectrumTextures() {
     a.N = N; a.C = C; a.nStates = 1;
     a.sc = make_spread_consts();
     for (int i = 0; i < C; ++i) a.casc[i] = make_cascade_consts(cascades[i]);
-    a.states = stateDev; a.noise = noise; a.h0 = h0; a.wave = wave; a.waveHot = waveHot;
+    a.states = stateDev; a.noise = noise; a.h0 = h0; a.wave = wave; a.waveHot = waveHot; a.h0c = h0c;
     OCEAN_CUDA(launch_init(a, stream));
     OCEAN_CUDA(cudaStreamSynchronize(stream));  // `sc` is stack memory
     spectrumReady = true;
@@ -350,23 +373,23 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     FrameArgs a{};
     a.N = N; a.layers = C; a.C = C;
     for (int i = 0; i < C; ++i) a.dk[i] = make_cascade_consts(cascades[i]).dk;
-    a.h0 = h0; a.waveHot = waveHot; a.rowsA = rowsA; a.rowsB = rowsB;
+    a.h0 = h0; a.waveHot = waveHot; a.h0c = h0c; a.rowsA = rowsA; a.rowsB = rowsB;
     a.disp = disp; a.deriv = deriv; a.turb = turb; a.twiddle = twiddle;
     a.time = time; a.lambda = params.lambda;
     a.foamDecay = expf(-2.0f);  // RF:29-30
     a.zeroFoam = foamZero ? 1 : 0;
-    a.rowsDone = rowsDone;
     a.l2Window = l2.l2Window; a.l2WindowBytes = l2.l2WindowBytes; a.l2HitRatio = l2.l2HitRatio;
-    if (which == 0 || which == 1) {
-        if (rowPasses != (uint64_t)frame) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
-        ++rowPasses;
-        a.rowsTarget = (unsigned long long)N * rowPasses;
+    const bool doRows = which == 0 || which == 1, doCols = which == 0 || which == 2;
+    if (doRows && rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
+    if (doCols && !doRows && !rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
+    workspace_stamp(ws, N, doRows, doCols, &a);
+    if (doRows) {
         OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
+        rowsPending = true;
     }
-    if (which == 0 || which == 2) {
-        if (rowPasses != (uint64_t)frame + 1) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
-        a.rowsTarget = (unsigned long long)N * rowPasses;
+    if (doCols) {
         OCEAN_CUDA(launch_cols(a, &colsMaps, stream));
+        rowsPending = false;
         foamZero = false;
         ++frame;
     }
@@ -464,7 +487,7 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, disp, deriv, turb, twiddle, stateDev, seedDev, rowsDone, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -486,8 +509,8 @@ struct OceanEnsemble {
     float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     Workspace* ws = nullptr;
     float2* waveHot = nullptr;
+    float2* h0c = nullptr;
     ColsTmaMaps colsMaps;
-    unsigned long long* rowsDone = nullptr;  // per-layer row counters, zeroed before every wave
     float2* twiddle = nullptr;
     // double-buffered parameter / result staging so consecutive waves overlap
     StateConsts* stateDev[2] = {nullptr, nullptr};
@@ -511,12 +534,12 @@ int OceanEnsemble::create() {
     OCEAN_CUDA(cudaMalloc(&noise, batch * t * sizeof(float2)));
     float4** arrs[] = {&h0, &wave, &disp, &deriv, &turb};
     for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
-    ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4));
+    ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4), batch * C);
     if (!ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
     rowsA = ws->planeA();
     rowsB = ws->planeB();
     OCEAN_CUDA(cudaMalloc(&waveHot, (size_t)batch * C * t * sizeof(float2)));
-    OCEAN_CUDA(cudaMalloc(&rowsDone, (size_t)batch * C * sizeof(unsigned long long)));
+    OCEAN_CUDA(cudaMalloc(&h0c, (size_t)batch * C * t * sizeof(float2)));
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
@@ -531,6 +554,7 @@ int OceanEnsemble::create() {
     }
     OCEAN_CUDA(configure_frame_kernels(N));
     OCEAN_CUDA(make_cols_maps(N, batch * C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
+
     return OCEAN_OK;
 }
 
@@ -539,7 +563,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
     ia.N = N; ia.C = C;
     ia.sc = make_spread_consts();
     for (int i = 0; i < C; ++i) ia.casc[i] = make_cascade_consts(cascades[i]);
-    ia.noise = noise; ia.h0 = h0; ia.wave = wave; ia.waveHot = waveHot;
+    ia.noise = noise; ia.h0 = h0; ia.wave = wave; ia.waveHot = waveHot; ia.h0c = h0c;
     int waveIdx = 0;
     int pendingBase[2] = {-1, -1}, pendingCount[2] = {0, 0};
     auto drain = [&](int b) {
@@ -572,15 +596,16 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         FrameArgs fa{};
         fa.N = N; fa.layers = nb * C; fa.C = C;
         for (int i = 0; i < C; ++i) fa.dk[i] = ia.casc[i].dk;
-        fa.h0 = h0; fa.waveHot = waveHot; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
+        fa.h0 = h0; fa.waveHot = waveHot; fa.h0c = h0c; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
         fa.twiddle = twiddle; fa.time = time;
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
-        fa.rowsDone = rowsDone;
-        fa.rowsTarget = (unsigned long long)N;
+        // a short last wave leaves the upper layers' counters behind: restart the counting per wave
+        ws->rowPasses = ws->colPasses = 0;
+        OCEAN_CUDA(cudaMemsetAsync(ws->counters, 0, (size_t)2 * ws->layers * sizeof(unsigned long long), stream));
+        workspace_stamp(ws, N, true, true, &fa);
         l2_window(device, ws, &fa);
-        OCEAN_CUDA(cudaMemsetAsync(rowsDone, 0, (size_t)nb * C * sizeof(unsigned long long), stream));
         OCEAN_CUDA(launch_rows(fa, stream, false));  // follows the init kernel: no early start
         OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
         OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
@@ -601,7 +626,7 @@ void OceanEnsemble::destroy() {
     if (stream) cudaStreamSynchronize(stream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, disp, deriv, turb, twiddle, rowsDone, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) {
@@ -788,8 +813,6 @@ int ocean_reset_foam(OceanHandle* h) {
     OCEAN_CUDA(cudaMemsetAsync(h->turb, 0, h->C * h->layerBytes4(), h->stream));
     h->foamZero = true;
     h->frame = 0;
-    h->rowPasses = 0;
-    OCEAN_CUDA(cudaMemsetAsync(h->rowsDone, 0, h->C * sizeof(unsigned long long), h->stream));
     return OCEAN_OK;
 }
 

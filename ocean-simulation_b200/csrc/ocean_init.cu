@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
         a.h0[p] = make_float4(tp.h.x, tp.h.y, tp.h.x, -tp.h.y);  // IS:141
         a.wave[p] = tp.wave;
         a.waveHot[p] = make_float2(tp.wave.y, tp.wave.w);
+        a.h0c[p] = tp.h;
         return;
     }
     const Texel tm = initial_spectrum_texel(mx, my, N, sc, cc, a.sc, __ldg(&noise[(size_t)my * N + mx]));
@@ -111,6 +112,8 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
     a.wave[m] = tm.wave;
     a.waveHot[p] = make_float2(tp.wave.y, tp.wave.w);
     a.waveHot[m] = make_float2(tm.wave.y, tm.wave.w);
+    a.h0c[p] = tp.h;
+    a.h0c[m] = tm.h;
 }
 
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s) {

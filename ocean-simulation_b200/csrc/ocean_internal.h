@@ -48,6 +48,7 @@ struct InitArgs {
     float4* h0;                        // device, [state*C + cascade][y][x]
     float4* wave;                      // (kx, 1/|k|, kz, omega): the reference's waveData layout (inspection / parity)
     float2* waveHot;                   // (1/|k|, omega): what the frame kernels read; kx, kz are recomputed as n*dk
+    float2* h0c;                       // h0(k) alone: the pair-row kernel reads it at k and at -k instead of the 16-byte packing
 };
 
 struct FrameArgs {
@@ -57,6 +58,7 @@ struct FrameArgs {
     float dk[OCEAN_MAX_CASCADES];      // 2*PI/wavelength per cascade (IS:110)
     const float4* h0;
     const float2* waveHot;             // (1/|k|, omega) [layer][y][x]
+    const float2* h0c;                 // h0(k) [layer][y][x] (compact copy of h0.xy)
     float4* rowsA;                     // (DxDz, DyDxz) after the x pass, [layer][y][x]
     float4* rowsB;                     // (DyxDyz, DxxDzz)
     float4* disp;
@@ -72,6 +74,11 @@ struct FrameArgs {
     // (acquire), so columns of the first layers overlap the row pass of the last ones.
     unsigned long long* rowsDone;      // device, one counter per layer
     unsigned long long rowsTarget;     // N * (row passes issued on these counters so far)
+    // Column -> row hand-back per layer (write-after-read on the workspace, and the turbulence chain):
+    // the column pass adds the columns it has finished AND stored to colsDone[layer]; a row CTA of the
+    // next frame may overwrite its rows of the workspace once colsDone[layer] >= colsTarget.
+    unsigned long long* colsDone;      // device, one counter per layer
+    unsigned long long colsTarget;     // N * (column passes issued before this frame)
     // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
     // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
     const void* l2Window;

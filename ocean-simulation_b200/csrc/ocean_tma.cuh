@@ -25,6 +25,16 @@ __device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long
     return v;
 }
 
+// Spin (one thread) until *flag >= target.  A lost producer must not hang the GPU: trap after ~1 s.
+__device__ __forceinline__ void spin_until_ge(const unsigned long long* flag, unsigned long long target) {
+    if (ld_acquire_gpu(flag) >= target) return;
+    const long long t0 = clock64();
+    while (ld_acquire_gpu(flag) < target) {
+        __nanosleep(32);
+        if (clock64() - t0 > (1ll << 31)) __trap();
+    }
+}
+
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }

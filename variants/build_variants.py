@@ -7,14 +7,9 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "tw4_m3": ["-DOCEAN_COLS512_TMA_W=4", "-DOCEAN_COLS512_TMA_MINB=3"],
-    "tw4_m2": ["-DOCEAN_COLS512_TMA_W=4", "-DOCEAN_COLS512_TMA_MINB=2"],
-    "tw2_m6": ["-DOCEAN_COLS512_TMA_W=2", "-DOCEAN_COLS512_TMA_MINB=6"],
-    "r_m12": ["-DOCEAN_ROWS512_MINB=12"],
-    "r_m10": ["-DOCEAN_ROWS512_MINB=10"],
-    "r_m7": ["-DOCEAN_ROWS512_MINB=7"],
-    "r2_m7": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
-    "r2_m4": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=4"],
+    "rp4": ["-DOCEAN_ROWPAIR_MINB=4"],
+    "leg": ["-DOCEAN_ROWS_USE_LEGACY"],
+    "c1_leg": ["-DOCEAN_COLS_TMA_CTAS_PER_SM=1", "-DOCEAN_COLS_TMA_MINB=1", "-DOCEAN_ROWS_USE_LEGACY"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
@@ -22,7 +17,7 @@ if __name__ == "__main__":
     names = sys.argv[1:] or list(VARIANTS)
     for n in names:
         obj = os.path.join(HERE, "frame_%s.o" % n)
-        cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + bm.COMMON + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
+        cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
         info = re.findall(r"ocean_(rows|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)

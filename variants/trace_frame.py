@@ -4,12 +4,13 @@ import ctypes, os, subprocess, sys
 import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__)); ROOT = os.path.dirname(HERE); sys.path.insert(0, ROOT)
 LIB = os.path.join(HERE, "lib_trace.so")
+EXTRA = [a for a in sys.argv[1:] if a.startswith("-D")]
 
 def build():
     import oceanpkg
     bm = oceanpkg.build_module(); bm.build()
     obj = os.path.join(HERE, "frame_trace.o")
-    subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + ["-DOCEAN_TRACE", "-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj])
+    subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + ["-DOCEAN_TRACE"] + EXTRA + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj])
     others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o")]
     subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", LIB, obj] + others)
     os.remove(obj)
