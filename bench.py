@@ -29,7 +29,7 @@ METRIC = "cascade_frames_per_sec"
 UNIT = "cascade-frames/s"
 WORKLOAD = "config3: 4 cascades x 512^2, U10=10 m/s, fetch=100 km, depth=20 m (TMA), swell=0.8, all outputs"
 ALG_BYTES_PER_TEXEL_CASCADE = 96  # h0 16 + waveData 16 + turbulence 16 in, 3 x 16 out
-INSTANCES = 4                     # rotated per step: 4 x ~117 MB working set > 126 MB L2
+INSTANCES = int(os.environ.get("OCEAN_BENCH_INSTANCES", "4"))  # rotated per step: 4 x ~117 MB working set > 126 MB L2
 
 
 class ClockSampler(threading.Thread):

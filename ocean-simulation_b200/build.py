@@ -21,7 +21,7 @@ UNITS = {
     "ocean_frame.cu": [],
     "ocean_host.cu": [],
 }
-HEADERS = ["ocean_internal.h", "ocean_fft.cuh", "../../include/oceanfft.h", "../../include/ocean_noise.h"]
+HEADERS = ["ocean_internal.h", "ocean_fft.cuh", "ocean_tma.cuh", "ocean_fused.cuh", "../../include/oceanfft.h", "../../include/ocean_noise.h"]
 
 
 def _nvcc():

@@ -383,6 +383,12 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     if (doRows && rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
     if (doCols && !doRows && !rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
     workspace_stamp(ws, N, doRows, doCols, &a);
+    if (which == 0 && frame_fused_available(N, &colsMaps)) {
+        OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
+        foamZero = false;
+        ++frame;
+        return OCEAN_OK;
+    }
     if (doRows) {
         OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
         rowsPending = true;
@@ -606,8 +612,12 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         OCEAN_CUDA(cudaMemsetAsync(ws->counters, 0, (size_t)2 * ws->layers * sizeof(unsigned long long), stream));
         workspace_stamp(ws, N, true, true, &fa);
         l2_window(device, ws, &fa);
-        OCEAN_CUDA(launch_rows(fa, stream, false));  // follows the init kernel: no early start
-        OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
+        if (frame_fused_available(N, &colsMaps)) {
+            OCEAN_CUDA(launch_frame(fa, &colsMaps, stream, false));  // follows the init kernel: no early start
+        } else {
+            OCEAN_CUDA(launch_rows(fa, stream, false));
+            OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
+        }
         OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
         OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
         OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));

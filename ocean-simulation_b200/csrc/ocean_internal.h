@@ -105,6 +105,9 @@ cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
 // legal when that kernel does not produce h0 / waveHot / twiddles (i.e. it is a column pass).
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early);
 cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s);
+// The whole frame as one persistent kernel (ocean_fused.cuh), where available (N = 256, 512).
+bool frame_fused_available(int N, const ColsTmaMaps* maps);
+cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,

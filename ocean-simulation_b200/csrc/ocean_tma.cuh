@@ -64,6 +64,17 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
                  "r"(smem_u32(smemSrc)), "r"(c0), "r"(c1)
                  : "memory");
 }
+// 1-D bulk copies (contiguous, 16-byte aligned, size a multiple of 16): global -> shared with byte-count
+// completion on an mbarrier, and shared -> global tracked by the issuing thread's bulk async-group.
+__device__ __forceinline__ void bulk_load_1d(void* smemDst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smemDst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smemSrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smemSrc)), "r"(bytes)
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // every committed bulk group has finished READING its shared-memory source (the buffer may be reused)
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

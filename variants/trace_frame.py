@@ -55,6 +55,15 @@ def main():
     first = g[1, :148, 2] > 0
     d = np.diff(c[1, :nc, 2:8], axis=1) / 1.965e3
     print("cols per-tile phase durations (us): " + ", ".join("%s %.2f" % (names[1][i + 3], np.median(d[:, i])) for i in range(5)))
+    # per-layer hand-off: last row CTA end vs first / last "A arrived" of the layer's column tiles
+    rows_per_layer = nr // 4
+    tiles_per_layer = nc // 4
+    for L in range(4):
+        re = (g[0, L * rows_per_layer:(L + 1) * rows_per_layer, 7] - t0) / 1e3
+        rs = (g[0, L * rows_per_layer:(L + 1) * rows_per_layer, 0] - t0) / 1e3
+        ca = (g[1, L * tiles_per_layer:(L + 1) * tiles_per_layer, 2] - t0) / 1e3
+        ce = (g[1, L * tiles_per_layer:(L + 1) * tiles_per_layer, 7] - t0) / 1e3
+        print("  layer %d: rows start %.1f..%.1f end %.1f..%.1f | cols A arrived %.1f..%.1f  tile end %.1f..%.1f" % (L, rs.min(), rs.max(), re.min(), re.max(), ca.min(), ca.max(), ce.min(), ce.max()))
     # CTAs per SM
     sm = smid[0, :nr]; print("rows CTAs per SM: min %d max %d" % (np.bincount(sm).min(), np.bincount(sm).max()))
 
