@@ -174,15 +174,24 @@ def run_cuda(args):
     barrier()
     launches = int(lib.ocean_launch_count() - launches0)
     ms = e0.elapsed_time(e1)
-    # ---- e2e: WaterBody.Update = frame + readback of displacement layer 0 to pinned host memory ----
-    barrier()
-    t0 = time.perf_counter()
-    for f in range(K):
-        bodies[f % INSTANCES].Update((W + K + f) / 60.0)
-    for b in bodies:
-        b.Sync()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
+    # ---- e2e: WaterBody.Update = frame + async readback to pinned host memory (WB:284-297), through the C ABI.
+    # Timed twice: shipping only the height channel GetWaterHeight consumes (headline), and the reference's
+    # whole-layer RGBA request.
+    def run_e2e(mode, base):
+        for b in bodies:
+            b.SetReadbackMode(mode)
+        barrier()
+        t0 = time.perf_counter()
+        for f in range(K):
+            bodies[f % INSTANCES].Update((base + f) / 60.0)
+        for b in bodies:
+            b.Sync()
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+    L = pkg._lib
+    run_e2e(L.READBACK_HEIGHT, W + K)  # warm the readback path (pinned buffers, events)
+    e2e_s = run_e2e(L.READBACK_HEIGHT, W + 2 * K)
+    e2e_rgba_s = run_e2e(L.READBACK_RGBA, W + 3 * K)
     clocks = sampler.summary()
     # ---- per-kernel durations (separate pass: an event between the two launches) ----
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
@@ -190,19 +199,19 @@ def run_cuda(args):
     for f in range(K):
         b = bodies[f % INSTANCES]
         evs[f][0].record(stream)
-        b.StepPartial((W + 2 * K + f) / 60.0, 1)
+        b.StepPartial((W + 4 * K + f) / 60.0, 1)
         evs[f][1].record(stream)
-        b.StepPartial((W + 2 * K + f) / 60.0, 2)
+        b.StepPartial((W + 4 * K + f) / 60.0, 2)
         evs[f][2].record(stream)
     torch.cuda.synchronize()
     rows_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
     cols_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
 
-    t_ms, t_e2e = ms, e2e_s
+    t_ms, t_e2e, t_e2e_rgba = ms, e2e_s, e2e_rgba_s
     if dist is not None:
-        t = torch.tensor([ms, e2e_s * 1e3], device="cuda", dtype=torch.float64)
+        t = torch.tensor([ms, e2e_s * 1e3, e2e_rgba_s * 1e3], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_ms, t_e2e = float(t[0]), float(t[1]) / 1e3
+        t_ms, t_e2e, t_e2e_rgba = float(t[0]), float(t[1]) / 1e3, float(t[2]) / 1e3
     describe = bodies[0].describe()
     for b in bodies:
         b.OnDisable()
@@ -228,9 +237,13 @@ def run_cuda(args):
                            INSTANCES, INSTANCES * (7 * 16 * N * N * C) / 1e6),
                        "kernels": describe},
             "e2e": {"value": world * K * C / t_e2e, "unit": UNIT, "h2d_bytes_per_step": 4,
-                    "d2h_bytes_per_step": N * N * 16, "ms_per_step": 1e3 * t_e2e / K,
-                    "what": "ocean_update through the C ABI: frame + async readback of displacement layer 0 to pinned host "
-                            "memory (WaterBody.Update WB:284-297); the only per-step host input is the time scalar"},
+                    "d2h_bytes_per_step": N * N * 4, "ms_per_step": 1e3 * t_e2e / K,
+                    "what": "ocean_update through the C ABI, host wall clock: frame + pack + async readback to pinned host "
+                            "memory of the height channel of displacement layer 0 (what GetWaterHeight WB:195-209 reads; "
+                            "WaterBody.Update WB:284-297); the only per-step host input is the time scalar",
+                    "rgba_readback": {"value": world * K * C / t_e2e_rgba, "ms_per_step": 1e3 * t_e2e_rgba / K,
+                                      "d2h_bytes_per_step": N * N * 16,
+                                      "what": "same with the reference's whole-layer RGBA32F request (WB:288), PCIe-bound"}},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

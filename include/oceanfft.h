@@ -133,8 +133,16 @@ int ocean_step_partial(OceanHandle* h, float time, int which);
  * layer 0 (WB:288) into library-owned pinned memory on a second stream.  The readback becomes
  * visible to OCEAN_QUERY_READBACK_REF / ocean_readback_ptr once it has completed. */
 int ocean_update(OceanHandle* h, float time);
-/* Latest completed readback (N*N*4 floats, RGBA of displacement layer 0) or NULL; *frame gets
- * the index of the frame it belongs to (-1 if none).  wait != 0 blocks for the newest request. */
+/* What ocean_update ships to the host.  RGBA = the whole displacement layer 0, N*N*16 B, exactly the
+ * reference's AsyncGPUReadback request (WB:288).  HEIGHT = only the channel GetWaterHeight consumes
+ * (`buoyancyData[index].g`, WB:206-208), packed on the device: N*N*4 B over PCIe.  Takes effect at the
+ * next ocean_update; OCEAN_QUERY_READBACK_REF answers identically in both modes. */
+typedef enum OceanReadbackMode { OCEAN_READBACK_RGBA = 0, OCEAN_READBACK_HEIGHT = 1 } OceanReadbackMode;
+int ocean_set_readback_mode(OceanHandle* h, int mode /*OceanReadbackMode*/);
+int ocean_readback_mode_of_latest(OceanHandle* h); /* mode the latest completed readback was made in, -1 if none */
+/* Latest completed readback or NULL: N*N*4 floats (RGBA of displacement layer 0) in RGBA mode, N*N
+ * floats (heights) in HEIGHT mode; *frame gets the index of the frame it belongs to (-1 if none).
+ * wait != 0 blocks for the newest request. */
 const float* ocean_readback_ptr(OceanHandle* h, int wait, int64_t* frame);
 
 /* ---- outputs: what WB:277-281 publishes to Water.shader ------------------------------------ */

@@ -12,6 +12,8 @@ OCEAN_MAX_CASCADES = 5
 OK, ERR_INVALID_ARGUMENT, ERR_INVALID_SIZE, ERR_INVALID_CASCADES, ERR_INVALID_PARAMS, ERR_CUDA, ERR_NOT_INITIALIZED = range(7)
 # OceanArray
 DISPLACEMENT, DERIVATIVES, TURBULENCE, INITIAL_SPECTRUM, WAVES_DATA, NOISE, ROW_SPECTRA = range(7)
+# OceanReadbackMode
+READBACK_RGBA, READBACK_HEIGHT = range(2)
 # OceanQueryMode
 QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCADES = range(4)
 
@@ -19,7 +21,7 @@ QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCAD
 ABI_SYMBOLS = [
     "ocean_abi_version", "ocean_last_error", "ocean_device_count", "ocean_create", "ocean_destroy",
     "ocean_set_params", "ocean_init_spectrum", "ocean_step", "ocean_step_partial", "ocean_sync", "ocean_update",
-    "ocean_readback_ptr", "ocean_get_output", "ocean_copy_output", "ocean_get_wavelengths",
+    "ocean_readback_ptr", "ocean_set_readback_mode", "ocean_readback_mode_of_latest", "ocean_get_output", "ocean_copy_output", "ocean_get_wavelengths",
     "ocean_set_turbulence", "ocean_reset_foam", "ocean_frame_index", "ocean_query_heights",
     "ocean_get_stream", "ocean_set_stream", "ocean_launch_count", "ocean_describe",
     "ocean_ensemble_create", "ocean_ensemble_destroy", "ocean_ensemble_run",
@@ -73,6 +75,8 @@ def load():
     L.ocean_update.argtypes = [vp, ctypes.c_float]
     L.ocean_readback_ptr.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_int64)]
     L.ocean_readback_ptr.restype = fp
+    L.ocean_set_readback_mode.argtypes = [vp, ctypes.c_int]
+    L.ocean_readback_mode_of_latest.argtypes = [vp]
     L.ocean_get_output.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     L.ocean_copy_output.argtypes = [vp, ctypes.c_int, ctypes.c_int, fp]
     L.ocean_get_wavelengths.argtypes = [vp, fp, ip]

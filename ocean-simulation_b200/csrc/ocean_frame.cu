@@ -739,6 +739,13 @@ __global__ void ocean_query_kernel(const QueryArgs q) {
     q.out[i] = h;
 }
 
+// Height channel (.y = Dy, what GetWaterHeight WB:206-208 reads as `.g`) of one displacement layer,
+// packed for the host readback: 4 B instead of 16 B per texel over PCIe.
+__global__ void ocean_pack_height_kernel(const float4* __restrict__ disp, float* __restrict__ out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __ldcg(&disp[i]).y;
+}
+
 // 64-bit sum of the fp32 bit patterns of one state's array (order-independent => deterministic)
 __global__ void ocean_checksum_kernel(const uint4* __restrict__ arr, size_t float4PerState, unsigned long long* out,
                                       int outStride) {
@@ -1021,6 +1028,12 @@ cudaError_t launch_query(const float4* disp, int N, int C, const float* waveleng
     q.disp = disp; q.pts = pts; q.out = out; q.N = N; q.C = C; q.n = n; q.mode = mode;
     for (int i = 0; i < OCEAN_MAX_CASCADES; ++i) q.wavelengths[i] = i < C ? wavelengths[i] : 1.0f;
     ocean_query_kernel<<<(n + 255) / 256, 256, 0, s>>>(q);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_height(const float4* disp, float* out, int n, cudaStream_t s) {
+    ocean_pack_height_kernel<<<(n + 255) / 256, 256, 0, s>>>(disp, out, n);
     count_launch();
     return cudaGetLastError();
 }

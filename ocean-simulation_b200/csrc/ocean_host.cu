@@ -282,6 +282,8 @@ struct OceanHandle {
     cudaEvent_t rbDone[RB] = {nullptr, nullptr, nullptr};
     cudaEvent_t rbSnap = nullptr;
     int64_t rbFrame[RB] = {-1, -1, -1};
+    int rbMode = OCEAN_READBACK_RGBA;             // what ocean_update ships to the host
+    int rbSlotMode[RB] = {0, 0, 0};               // layout of each slot's host copy
     bool rbPending[RB] = {false, false, false};
     int rbLatest = -1;  // slot of the newest completed readback
     // query scratch
@@ -431,11 +433,18 @@ int OceanHandle::Update(float time) {
         OCEAN_CUDA(cudaEventSynchronize(rbDone[oldest]));
     }
     // snapshot layer 0 on the compute stream, ship it to the host on the copy stream
-    OCEAN_CUDA(cudaMemcpyAsync(rbStage[s], disp, layerBytes4(), cudaMemcpyDeviceToDevice, stream));
+    size_t bytes = layerBytes4();
+    if (rbMode == OCEAN_READBACK_HEIGHT) {
+        bytes = texels() * sizeof(float);
+        OCEAN_CUDA(launch_pack_height(disp, (float*)rbStage[s], (int)texels(), stream));
+    } else {
+        OCEAN_CUDA(cudaMemcpyAsync(rbStage[s], disp, bytes, cudaMemcpyDeviceToDevice, stream));
+    }
     OCEAN_CUDA(cudaEventRecord(rbSnap, stream));
     OCEAN_CUDA(cudaStreamWaitEvent(copyStream, rbSnap, 0));
-    OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], layerBytes4(), cudaMemcpyDeviceToHost, copyStream));
+    OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], bytes, cudaMemcpyDeviceToHost, copyStream));
     OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
+    rbSlotMode[s] = rbMode;
     rbFrame[s] = frame - 1;
     rbPending[s] = true;
     return OCEAN_OK;
@@ -449,6 +458,7 @@ int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* he
         if (ptsDev || outDev) return fail(OCEAN_ERR_INVALID_ARGUMENT, "READBACK_REF works on host buffers");
         PollReadbacks(false);
         const float* data = rbLatest >= 0 ? rbHost[rbLatest] : nullptr;
+        const bool packed = rbLatest >= 0 && rbSlotMode[rbLatest] == OCEAN_READBACK_HEIGHT;
         for (int i = 0; i < n; ++i) {
             if (!data) { heights[i] = 0.0f; continue; }
             const float lo = (float)(-(N / 2)), hi = (float)(N / 2);
@@ -458,7 +468,7 @@ int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* he
             int x = (int)(u * (float)N), y = (int)(v * (float)N);
             x = x < 0 ? 0 : (x > N - 1 ? N - 1 : x);
             y = y < 0 ? 0 : (y > N - 1 ? N - 1 : y);
-            heights[i] = data[((size_t)y * N + x) * 4 + 1];
+            heights[i] = packed ? data[(size_t)y * N + x] : data[((size_t)y * N + x) * 4 + 1];  // .g  WB:206-208
         }
         return OCEAN_OK;
     }
@@ -748,6 +758,8 @@ int ocean_sync(OceanHandle* h) {
     return OCEAN_OK;
 }
 
+int ocean_readback_mode_of_latest(OceanHandle* h) { return h && h->rbLatest >= 0 ? h->rbSlotMode[h->rbLatest] : -1; }
+
 const float* ocean_readback_ptr(OceanHandle* h, int wait, int64_t* frame) {
     if (frame) *frame = -1;
     if (!h) return nullptr;
@@ -756,6 +768,13 @@ const float* ocean_readback_ptr(OceanHandle* h, int wait, int64_t* frame) {
     if (h->rbLatest < 0) return nullptr;
     if (frame) *frame = h->rbFrame[h->rbLatest];
     return h->rbHost[h->rbLatest];
+}
+
+int ocean_set_readback_mode(OceanHandle* h, int mode) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    if (mode != OCEAN_READBACK_RGBA && mode != OCEAN_READBACK_HEIGHT) return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown readback mode %d", mode);
+    h->rbMode = mode;
+    return OCEAN_OK;
 }
 
 static int pick_array(OceanHandle* h, int which, void** p, size_t* bytes) {

@@ -110,6 +110,7 @@ bool frame_fused_available(int N, const ColsTmaMaps* maps);
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
+cudaError_t launch_pack_height(const float4* dispLayer, float* out, int n, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
                             int outStride, cudaStream_t s);
 cudaError_t configure_frame_kernels(int N);  // opt in to >48 KiB dynamic shared memory where needed

@@ -154,14 +154,20 @@ class WaterBody:
         L.check(self._lib.ocean_query_heights(self._need(), pts.ctypes.data, pts.shape[0], int(mode), out.ctypes.data, 0, 0))
         return out
 
+    def SetReadbackMode(self, mode):
+        """L.READBACK_RGBA (the reference's whole-layer request, default) or L.READBACK_HEIGHT (packed .g only)."""
+        L.check(self._lib.ocean_set_readback_mode(self._need(), int(mode)))
+
     def WaitReadback(self):
-        """Blocks for the newest AsyncGPUReadback; returns (frame, [N][N][4] array) or (-1, None)."""
+        """Blocks for the newest AsyncGPUReadback; returns (frame, array) or (-1, None).  The array is
+        [N][N][4] in RGBA mode and [N][N] (heights) in HEIGHT mode."""
         fr = ctypes.c_int64(-1)
         p = self._lib.ocean_readback_ptr(self._need(), 1, ctypes.byref(fr))
         if not p:
             return -1, None
         N = self.texturesSize
-        return fr.value, np.ctypeslib.as_array(p, shape=(N, N, 4)).copy()
+        packed = self._lib.ocean_readback_mode_of_latest(self._need()) == L.READBACK_HEIGHT
+        return fr.value, np.ctypeslib.as_array(p, shape=(N, N) if packed else (N, N, 4)).copy()
 
     # -- arrays ----------------------------------------------------------------------------
     def _array(self, which, cascade=-1):

@@ -326,6 +326,25 @@ def test_update_readback_and_get_water_height(pkg, po):
     body.OnDisable()
 
 
+def test_height_only_readback_answers_like_the_rgba_readback(pkg, po):
+    """OCEAN_READBACK_HEIGHT ships only `.g` of layer 0 (what WB:206-208 reads); GetWaterHeight is unchanged."""
+    cfg = pkg.scene.config(1)
+    body, _ = make_body(pkg, po, cfg, N=128)
+    L = pkg._lib
+    pts = [(3.0, 0.0, -7.0), (-63.5, 0.0, 63.9), (0.0, 0.0, 0.0), (500.0, 0.0, -500.0)]
+    body.Update(0.5)
+    frame, rgba = body.WaitReadback()
+    assert frame == 0 and rgba.shape == (128, 128, 4)
+    want = [body.GetWaterHeight(p) for p in pts]
+    body.SetReadbackMode(L.READBACK_HEIGHT)
+    body.Update(0.5)  # same time: same displacement (only the foam recursion advances)
+    frame, h = body.WaitReadback()
+    assert frame == 1 and h.shape == (128, 128)
+    assert np.array_equal(h, rgba[..., 1]) and np.array_equal(h, body.displacementsTextures[0][..., 1])
+    assert [body.GetWaterHeight(p) for p in pts] == want
+    body.OnDisable()
+
+
 def test_choppiness_lambda(pkg, po):
     """lambda scales the horizontal displacement and enters the Jacobian; lambda = 1 is the reference."""
     cfg = pkg.scene.config(1)

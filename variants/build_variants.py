@@ -7,9 +7,11 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "rp4": ["-DOCEAN_ROWPAIR_MINB=4"],
-    "leg": ["-DOCEAN_ROWS_USE_LEGACY"],
-    "c1_leg": ["-DOCEAN_COLS_TMA_CTAS_PER_SM=1", "-DOCEAN_COLS_TMA_MINB=1", "-DOCEAN_ROWS_USE_LEGACY"],
+    "rb7": ["-DOCEAN_ROWS512_MAXB=7"],
+    "rb8": ["-DOCEAN_ROWS512_MAXB=8"],
+    "rb10": ["-DOCEAN_ROWS512_MAXB=10"],
+    "rb7_m7": ["-DOCEAN_ROWS512_MAXB=7", "-DOCEAN_ROWS512_MINB=7"],
+    "rb5_m7": ["-DOCEAN_ROWS512_MAXB=5", "-DOCEAN_ROWS512_MINB=7"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
