@@ -91,8 +91,13 @@ typedef enum OceanQueryMode {
     OCEAN_QUERY_NEAREST_REF = 0,          /* WaterBody.GetWaterHeight WB:195-209, bit-exact, on the current frame */
     OCEAN_QUERY_READBACK_REF = 1,         /* same lookup, but in the last completed readback: 0 until one exists (WB:197) */
     OCEAN_QUERY_BILINEAR = 2,             /* extension: cascade 0, uv = world/wavelength[0] (Water.shader:325), bilinear, Repeat wrap */
-    OCEAN_QUERY_BILINEAR_ALL_CASCADES = 3 /* extension: sum over cascades, as the surface shader displaces vertices */
+    OCEAN_QUERY_BILINEAR_ALL_CASCADES = 3, /* extension: sum over cascades, as the surface shader displaces vertices */
+    OCEAN_QUERY_DISPLACED = 4             /* extension: height of the surface ABOVE (x, z).  Water.shader:327 moves a vertex
+                                             horizontally too, so the point over (x, z) started at q with q + Dxz(q) = (x, z);
+                                             solved by OCEAN_DISPLACED_ITERATIONS fixed-point steps q <- (x, z) - Dxz(q), all
+                                             cascades, bilinear; returns Dy(q) */
 } OceanQueryMode;
+#define OCEAN_DISPLACED_ITERATIONS 4
 
 typedef struct OceanHandle OceanHandle;     /* one WaterBody: C cascades of N x N on one device */
 typedef struct OceanEnsemble OceanEnsemble; /* pooled batch runner for many independent oceans */
@@ -152,6 +157,32 @@ int ocean_get_output(OceanHandle* h, int which /*OceanArray*/, void** devPtr, si
 /* Synchronous copy of one layer (cascade) to host memory; cascade = -1 copies all layers. */
 int ocean_copy_output(OceanHandle* h, int which /*OceanArray*/, int cascade, float* host);
 int ocean_get_wavelengths(OceanHandle* h, float* out /*[nCascades]*/, int* nCascades); /* _Wavelengths WB:281 */
+
+/* ---- consumers of the arrays: mip chain WB:191-192, Water.shader Domain/Fragment arithmetic ---- */
+
+/* derivativesTextures.GenerateMips(); turbulenceTextures.GenerateMips() (WB:191-192) for the current frame.
+ * The displacement array has no chain (WB:227).  Levels 1..log2(N), 2x2 box filter (Unity's filter is not
+ * part of the reference tree; the box filter is this library's definition).  Off the frame's hot path:
+ * explicit, or every frame after ocean_set_auto_mips(h, 1), or on demand by ocean_sample_surface(lod > 0). */
+int ocean_generate_mips(OceanHandle* h);
+int ocean_set_auto_mips(OceanHandle* h, int enabled);
+int ocean_mip_levels(OceanHandle* h); /* log2(N) */
+/* Device pointer of a chain: [layer][levels 1..log2(N) packed one after another], (N*N-1)/3 texels per layer. */
+int ocean_get_mips(OceanHandle* h, int which /*OCEAN_DERIVATIVES | OCEAN_TURBULENCE*/, void** devPtr, size_t* bytes);
+/* Synchronous copy of one level of one layer, (N>>level)^2 * 4 floats; level 0 is the array itself. */
+int ocean_copy_mip(OceanHandle* h, int which, int level, int cascade, float* host);
+
+/* What Water.shader derives from the arrays at n world positions (x, z), uv_i = worldXZ / wavelength_i,
+ * sampler = Repeat + trilinear (WB:104-128), `lod` as the shader's lodLevel:
+ *   displacement[3n] = sum_i disp_i(uv_i)                                   Domain   WS:322-327
+ *   normal[3n]       = normalize(-sx, 1, -sz), (sx, sz) = (d.x/(1+d.z), d.y/(1+d.w)),
+ *                      d = sum_i deriv_i(uv_i, lod)                         Fragment WS:337-347
+ *   foam[n]          = sum_i (1 - saturate(turb_i(uv_i, lod).x))            Fragment WS:343 (compared with
+ *                      _FoamThreshold at WS:371)
+ * Any output pointer may be NULL.  onDevice != 0: every pointer is a device pointer and the call is
+ * asynchronous on the handle's stream; otherwise host buffers and the call returns when they are filled. */
+int ocean_sample_surface(OceanHandle* h, const float* worldXZ, int n, float lod, float* displacement, float* normal,
+                         float* foam, int onDevice);
 
 /* ---- foam state: the persistence implicit in the turbulence RenderTexture RF:28,32 --------- */
 int ocean_set_turbulence(OceanHandle* h, const float* host /* C*N*N*4 */);

@@ -15,7 +15,8 @@ DISPLACEMENT, DERIVATIVES, TURBULENCE, INITIAL_SPECTRUM, WAVES_DATA, NOISE, ROW_
 # OceanReadbackMode
 READBACK_RGBA, READBACK_HEIGHT = range(2)
 # OceanQueryMode
-QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCADES = range(4)
+QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCADES, QUERY_DISPLACED = range(5)
+DISPLACED_ITERATIONS = 4
 
 # every symbol include/oceanfft.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = [
@@ -26,6 +27,8 @@ ABI_SYMBOLS = [
     "ocean_get_stream", "ocean_set_stream", "ocean_launch_count", "ocean_describe",
     "ocean_ensemble_create", "ocean_ensemble_destroy", "ocean_ensemble_run",
     "ocean_ensemble_get_output", "ocean_ensemble_copy_output",
+    "ocean_generate_mips", "ocean_set_auto_mips", "ocean_mip_levels", "ocean_get_mips", "ocean_copy_mip",
+    "ocean_sample_surface",
 ]
 
 
@@ -97,6 +100,12 @@ def load():
                                      ctypes.c_float, ctypes.POINTER(ctypes.c_uint64)]
     L.ocean_ensemble_get_output.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     L.ocean_ensemble_copy_output.argtypes = [vp, ctypes.c_int, ctypes.c_int, fp]
+    L.ocean_generate_mips.argtypes = [vp]
+    L.ocean_set_auto_mips.argtypes = [vp, ctypes.c_int]
+    L.ocean_mip_levels.argtypes = [vp]
+    L.ocean_get_mips.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
+    L.ocean_copy_mip.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, fp]
+    L.ocean_sample_surface.argtypes = [vp, vp, ctypes.c_int, ctypes.c_float, vp, vp, vp, ctypes.c_int]
     _lib = L
     return L
 

@@ -19,6 +19,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=o
 UNITS = {
     "ocean_init.cu": ["-fmad=false"],
     "ocean_frame.cu": [],
+    "ocean_surface.cu": ["-fmad=false"],  # sampler / shading arithmetic: bit-comparable with the fp32 oracle
     "ocean_host.cu": [],
 }
 HEADERS = ["ocean_internal.h", "ocean_fft.cuh", "ocean_tma.cuh", "ocean_fused.cuh", "../../include/oceanfft.h", "../../include/ocean_noise.h"]

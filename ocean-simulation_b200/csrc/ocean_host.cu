@@ -290,6 +290,13 @@ struct OceanHandle {
     float2* qPts = nullptr;
     float* qOut = nullptr;
     int qCap = 0;
+    // mip chains of the derivative and turbulence arrays (WB:191-192), allocated on first use
+    float4 *derivMips = nullptr, *turbMips = nullptr;
+    int64_t mipsFrame = -1;  // frame index the chains were built from
+    bool autoMips = false;   // rebuild them at the end of every frame, as the reference does
+    // surface-sample scratch: n x (2 in + 7 out) floats
+    float* sBuf = nullptr;
+    int sCap = 0;
 
     size_t texels() const { return (size_t)N * N; }
     size_t layerBytes4() const { return texels() * sizeof(float4); }
@@ -301,6 +308,8 @@ struct OceanHandle {
     void PollReadbacks(bool wait);
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
     int AttachWorkspace(cudaStream_t shared);
+    int GenerateMips();
+    int SampleSurface(const float* worldXZ, int n, float lod, float* disp3, float* normal3, float* foam, bool onDevice);
     void OnDisable();
 };
 
@@ -389,7 +398,7 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
         OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
         foamZero = false;
         ++frame;
-        return OCEAN_OK;
+        return autoMips ? GenerateMips() : OCEAN_OK;
     }
     if (doRows) {
         OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
@@ -400,7 +409,52 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
         rowsPending = false;
         foamZero = false;
         ++frame;
+        if (autoMips) return GenerateMips();
     }
+    return OCEAN_OK;
+}
+
+// derivativesTextures.GenerateMips(); turbulenceTextures.GenerateMips();   WB:191-192
+int OceanHandle::GenerateMips() {
+    const size_t bytes = (size_t)C * mip_texels_per_layer(N) * sizeof(float4);
+    if (!derivMips) OCEAN_CUDA(cudaMalloc(&derivMips, bytes));
+    if (!turbMips) OCEAN_CUDA(cudaMalloc(&turbMips, bytes));
+    OCEAN_CUDA(launch_mip_chain(deriv, derivMips, N, C, stream));
+    OCEAN_CUDA(launch_mip_chain(turb, turbMips, N, C, stream));
+    mipsFrame = frame;
+    return OCEAN_OK;
+}
+
+// Water.shader Domain (WS:322-327) + Fragment (WS:337-347) arithmetic for n world positions.
+int OceanHandle::SampleSurface(const float* worldXZ, int n, float lod, float* disp3, float* normal3, float* foam, bool onDevice) {
+    if (n == 0) return OCEAN_OK;
+    if (lod > 0.0f && (normal3 || foam) && mipsFrame != frame) {  // trilinear reads need the current frame's chain
+        int rc = GenerateMips();
+        if (rc != OCEAN_OK) return rc;
+    }
+    const bool useMips = lod > 0.0f && mipsFrame == frame;
+    float wl[OCEAN_MAX_CASCADES];
+    for (int i = 0; i < C; ++i) wl[i] = cascades[i].wavelength;
+    if (onDevice) {
+        OCEAN_CUDA(launch_surface(disp, deriv, turb, useMips ? derivMips : nullptr, useMips ? turbMips : nullptr, N, C, wl,
+                                  (const float2*)worldXZ, n, lod, disp3, normal3, foam, stream));
+        return OCEAN_OK;
+    }
+    if (n > sCap) {
+        if (sBuf) cudaFree(sBuf);
+        sBuf = nullptr; sCap = 0;
+        OCEAN_CUDA(cudaMalloc(&sBuf, (size_t)n * 9 * sizeof(float)));
+        sCap = n;
+    }
+    float *dPts = sBuf, *dDisp = sBuf + (size_t)2 * n, *dNormal = dDisp + (size_t)3 * n, *dFoam = dNormal + (size_t)3 * n;
+    OCEAN_CUDA(cudaMemcpyAsync(dPts, worldXZ, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, stream));
+    OCEAN_CUDA(launch_surface(disp, deriv, turb, useMips ? derivMips : nullptr, useMips ? turbMips : nullptr, N, C, wl,
+                              (const float2*)dPts, n, lod, disp3 ? dDisp : nullptr, normal3 ? dNormal : nullptr,
+                              foam ? dFoam : nullptr, stream));
+    if (disp3) OCEAN_CUDA(cudaMemcpyAsync(disp3, dDisp, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    if (normal3) OCEAN_CUDA(cudaMemcpyAsync(normal3, dNormal, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    if (foam) OCEAN_CUDA(cudaMemcpyAsync(foam, dFoam, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    OCEAN_CUDA(cudaStreamSynchronize(stream));
     return OCEAN_OK;
 }
 
@@ -488,7 +542,11 @@ int OceanHandle::GetWaterHeight(const float* worldXZ, int n, int mode, float* he
     float* out = outDev ? heights : qOut;
     float wl[OCEAN_MAX_CASCADES];
     for (int i = 0; i < C; ++i) wl[i] = cascades[i].wavelength;
-    OCEAN_CUDA(launch_query(disp, N, C, wl, pts, out, n, mode, stream));
+    if (mode == OCEAN_QUERY_DISPLACED) {
+        OCEAN_CUDA(launch_displaced_query(disp, N, C, wl, pts, out, n, OCEAN_DISPLACED_ITERATIONS, stream));
+    } else {
+        OCEAN_CUDA(launch_query(disp, N, C, wl, pts, out, n, mode, stream));
+    }
     if (!outDev) {
         OCEAN_CUDA(cudaMemcpyAsync(heights, qOut, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
         OCEAN_CUDA(cudaStreamSynchronize(stream));
@@ -503,7 +561,7 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -851,9 +909,73 @@ int ocean_query_heights(OceanHandle* h, const float* worldXZ, int n, int mode, f
                         int heightsOnDevice) {
     if (!h || (n > 0 && (!worldXZ || !heights))) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
     if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
-    if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_BILINEAR_ALL_CASCADES) return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown query mode %d", mode);
+    if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_DISPLACED) return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown query mode %d", mode);
     DeviceScope scope(h->device);
     return h->GetWaterHeight(worldXZ, n, mode, heights, pointsOnDevice != 0, heightsOnDevice != 0);
+}
+
+int ocean_generate_mips(OceanHandle* h) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    DeviceScope scope(h->device);
+    return h->GenerateMips();
+}
+
+int ocean_set_auto_mips(OceanHandle* h, int enabled) {
+    if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
+    h->autoMips = enabled != 0;
+    return OCEAN_OK;
+}
+
+int ocean_mip_levels(OceanHandle* h) {
+    if (!h) return -1;
+    int levels = 0;
+    while ((h->N >> levels) > 1) ++levels;
+    return levels;
+}
+
+static int mip_pick(OceanHandle* h, int which, float4** base, float4** mips) {
+    if (which == OCEAN_DERIVATIVES) { *base = h->deriv; *mips = h->derivMips; return OCEAN_OK; }
+    if (which == OCEAN_TURBULENCE) { *base = h->turb; *mips = h->turbMips; return OCEAN_OK; }
+    return fail(OCEAN_ERR_INVALID_ARGUMENT, "array %d has no mip chain (only OCEAN_DERIVATIVES and OCEAN_TURBULENCE do, WB:191-192)", which);
+}
+
+int ocean_get_mips(OceanHandle* h, int which, void** devPtr, size_t* bytes) {
+    if (!h || !devPtr || !bytes) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    float4 *base, *mips;
+    int rc = mip_pick(h, which, &base, &mips);
+    if (rc != OCEAN_OK) return rc;
+    if (!mips) return fail(OCEAN_ERR_NOT_INITIALIZED, "no mip chain yet: call ocean_generate_mips first");
+    *devPtr = mips;
+    *bytes = (size_t)h->C * mip_texels_per_layer(h->N) * sizeof(float4);
+    return OCEAN_OK;
+}
+
+int ocean_copy_mip(OceanHandle* h, int which, int level, int cascade, float* host) {
+    if (!h || !host) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (cascade < 0 || cascade >= h->C) return fail(OCEAN_ERR_INVALID_ARGUMENT, "cascade %d outside [0, %d)", cascade, h->C);
+    const int levels = ocean_mip_levels(h);
+    if (level < 0 || level > levels) return fail(OCEAN_ERR_INVALID_ARGUMENT, "level %d outside [0, %d]", level, levels);
+    float4 *base, *mips;
+    int rc = mip_pick(h, which, &base, &mips);
+    if (rc != OCEAN_OK) return rc;
+    if (level > 0 && !mips) return fail(OCEAN_ERR_NOT_INITIALIZED, "no mip chain yet: call ocean_generate_mips first");
+    DeviceScope scope(h->device);
+    const size_t n = (size_t)(h->N >> level);
+    const float4* src = level == 0 ? base + (size_t)cascade * h->texels()
+                                   : mips + (size_t)cascade * mip_texels_per_layer(h->N) + mip_level_offset(h->N, level);
+    OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    OCEAN_CUDA(cudaMemcpy(host, src, n * n * sizeof(float4), cudaMemcpyDeviceToHost));
+    return OCEAN_OK;
+}
+
+int ocean_sample_surface(OceanHandle* h, const float* worldXZ, int n, float lod, float* displacement, float* normal, float* foam,
+                         int onDevice) {
+    if (!h || (n > 0 && !worldXZ)) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
+    if (!(lod >= 0.0f)) return fail(OCEAN_ERR_INVALID_ARGUMENT, "lod must be >= 0");
+    if (n > 0 && !displacement && !normal && !foam) return fail(OCEAN_ERR_INVALID_ARGUMENT, "no output requested");
+    DeviceScope scope(h->device);
+    return h->SampleSurface(worldXZ, n, lod, displacement, normal, foam, onDevice != 0);
 }
 
 int ocean_get_stream(OceanHandle* h, void** s) {

@@ -110,6 +110,18 @@ bool frame_fused_available(int N, const ColsTmaMaps* maps);
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
+// ocean_surface.cu: mip chain (WB:191-192), surface shading inputs (Water.shader:322-347), displaced queries
+inline size_t mip_texels_per_layer(int N) { return ((size_t)N * N - 1) / 3; }  // levels 1..log2(N), packed
+inline size_t mip_level_offset(int N, int level) {                            // texel offset of `level` >= 1 inside a layer
+    const size_t m = (size_t)(N >> (level - 1));
+    return ((size_t)N * N - m * m) / 3;
+}
+cudaError_t launch_mip_chain(const float4* base, float4* mips, int N, int layers, cudaStream_t s);
+cudaError_t launch_surface(const float4* disp, const float4* deriv, const float4* turb, const float4* derivMips, const float4* turbMips,
+                           int N, int C, const float* wavelengths /*host, C*/, const float2* pts, int n, float lod, float* outDisp,
+                           float* outNormal, float* outFoam, cudaStream_t s);
+cudaError_t launch_displaced_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
+                                   float* out, int n, int iterations, cudaStream_t s);
 cudaError_t launch_pack_height(const float4* dispLayer, float* out, int n, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
                             int outStride, cudaStream_t s);

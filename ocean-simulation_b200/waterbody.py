@@ -154,6 +154,38 @@ class WaterBody:
         L.check(self._lib.ocean_query_heights(self._need(), pts.ctypes.data, pts.shape[0], int(mode), out.ctypes.data, 0, 0))
         return out
 
+    # -- consumers of the arrays -----------------------------------------------
+    def GenerateMips(self, auto=None):
+        """derivativesTextures.GenerateMips(); turbulenceTextures.GenerateMips()  (WB:191-192).
+        auto=True/False switches the per-frame rebuild the reference does on or off."""
+        if auto is not None:
+            L.check(self._lib.ocean_set_auto_mips(self._need(), 1 if auto else 0))
+        L.check(self._lib.ocean_generate_mips(self._need()))
+
+    @property
+    def mipLevels(self):
+        return self._lib.ocean_mip_levels(self._need())
+
+    def Mip(self, which, level, cascade):
+        """One level of one layer of a mipped array: [(N>>level)][(N>>level)][4]."""
+        n = self.texturesSize >> level
+        out = np.empty((n, n, 4), np.float32)
+        L.check(self._lib.ocean_copy_mip(self._need(), int(which), int(level), int(cascade),
+                                         out.ctypes.data_as(ctypes.POINTER(ctypes.c_float))))
+        return out
+
+    def SampleSurface(self, worldXZ, lod=0.0, displacement=True, normal=True, foam=True):
+        """Water.shader's Domain (WS:322-327) and Fragment (WS:337-347) arithmetic at world positions
+        [n][2]: returns (displacement [n][3] | None, normal [n][3] | None, foam [n] | None)."""
+        pts = np.ascontiguousarray(worldXZ, np.float32).reshape(-1, 2)
+        n = pts.shape[0]
+        d = np.empty((n, 3), np.float32) if displacement else None
+        nr = np.empty((n, 3), np.float32) if normal else None
+        f = np.empty(n, np.float32) if foam else None
+        ptr = lambda a: a.ctypes.data if a is not None else None
+        L.check(self._lib.ocean_sample_surface(self._need(), pts.ctypes.data, n, float(lod), ptr(d), ptr(nr), ptr(f), 0))
+        return d, nr, f
+
     def SetReadbackMode(self, mode):
         """L.READBACK_RGBA (the reference's whole-layer request, default) or L.READBACK_HEIGHT (packed .g only)."""
         L.check(self._lib.ocean_set_readback_mode(self._need(), int(mode)))

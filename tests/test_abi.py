@@ -71,6 +71,9 @@ def test_argument_validation_precedes_cuda(pkg):
     assert lib.ocean_create(None, good_c, 1, None, 0, 0, ctypes.byref(ctypes.c_void_p())) == L.ERR_INVALID_ARGUMENT
     assert lib.ocean_create(ctypes.byref(P()), good_c, 1, None, 0, 0, None) == L.ERR_INVALID_ARGUMENT
     assert lib.ocean_step(None, 0.0) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_generate_mips(None) == L.ERR_INVALID_ARGUMENT and lib.ocean_set_auto_mips(None, 1) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_mip_levels(None) == -1
+    assert lib.ocean_sample_surface(None, None, 0, 0.0, None, None, None, 0) == L.ERR_INVALID_ARGUMENT
     e = ctypes.c_void_p()
     assert lib.ocean_ensemble_create(100, good_c, 3, 4, 0, ctypes.byref(e)) == L.ERR_INVALID_SIZE
     assert lib.ocean_ensemble_create(256, good_c, 3, 0, 0, ctypes.byref(e)) == L.ERR_INVALID_ARGUMENT

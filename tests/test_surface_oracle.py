@@ -1,0 +1,113 @@
+"""The surface-consumer oracle (oracle/surface_oracle.py) against closed forms: sampler conventions of
+WaterBody.cs:104-128, the mip chain of WB:191-192 (box filter), Water.shader:322-347 arithmetic and the
+displaced-height inversion.  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import surface_oracle as so
+
+F = np.float32
+
+
+def test_bilinear_sampler_conventions():
+    n = 8
+    rng = np.random.default_rng(0)
+    img = rng.standard_normal((n, n, 4)).astype(F)
+    # texel centres return the texel
+    i = np.arange(n)
+    u = ((i + 0.5) / n).astype(F)
+    got = so.sample_bilinear(img, u, np.full(n, 2.5 / n, F))
+    assert np.array_equal(got, img[2, i])
+    # half way between two centres: the mean; across the edge: Repeat wrap
+    got = so.sample_bilinear(img, np.array([3.0 / n, 0.0], F), np.array([4.5 / n, 4.5 / n], F))
+    assert np.allclose(got[0], 0.5 * (img[4, 2] + img[4, 3]), atol=1e-6)
+    assert np.allclose(got[1], 0.5 * (img[4, n - 1] + img[4, 0]), atol=1e-6)
+    # uv outside [0, 1) wraps
+    a = so.sample_lod([img], np.array([0.3], F), np.array([0.7], F), 0.0)
+    b = so.sample_lod([img], np.array([-3.7], F), np.array([5.7], F), 0.0)
+    assert np.allclose(a, b, atol=2e-5)
+
+
+def test_mip_chain_is_the_box_filter():
+    img = np.arange(4 * 4 * 4, dtype=F).reshape(4, 4, 4)
+    lv = so.mip_chain(img)
+    assert [l.shape[0] for l in lv] == [4, 2, 1]
+    assert np.array_equal(lv[1][0, 0], (img[0, 0] + img[0, 1] + img[1, 0] + img[1, 1]) / 4)
+    assert np.array_equal(lv[1][1, 0], (img[2, 0] + img[2, 1] + img[3, 0] + img[3, 1]) / 4)
+    assert np.allclose(lv[2][0, 0], img.reshape(-1, 4).mean(0))
+    # the mean is preserved level to level
+    rng = np.random.default_rng(1)
+    lv = so.mip_chain(rng.standard_normal((64, 64, 4)).astype(F))
+    for a, b in zip(lv[:-1], lv[1:]):
+        assert np.allclose(a.reshape(-1, 4).mean(0), b.reshape(-1, 4).mean(0), atol=1e-5)
+
+
+def test_trilinear_blends_two_levels():
+    rng = np.random.default_rng(2)
+    lv = so.mip_chain(rng.standard_normal((16, 16, 4)).astype(F))
+    u, v = rng.random(50).astype(F), rng.random(50).astype(F)
+    s1, s2 = so.sample_bilinear(lv[1], u, v), so.sample_bilinear(lv[2], u, v)
+    assert np.array_equal(so.sample_lod(lv, u, v, 1.0), s1)
+    assert np.allclose(so.sample_lod(lv, u, v, 1.25), s1 + (s2 - s1) * 0.25, atol=1e-6)
+    # beyond the last level: clamps to the 1x1 level; a texture without a chain ignores the LOD
+    assert np.allclose(so.sample_lod(lv, u, v, 99.0), np.broadcast_to(lv[-1][0, 0], (50, 4)), atol=0)
+    assert np.array_equal(so.sample_lod(lv[:1], u, v, 3.0), so.sample_bilinear(lv[0], u, v))
+
+
+def test_surface_closed_forms():
+    """Constant arrays: Water.shader:322-347 collapses to closed forms."""
+    C, N = 3, 16
+    disp = np.zeros((C, N, N, 4), F)
+    deriv = np.zeros((C, N, N, 4), F)
+    turb = np.zeros((C, N, N, 4), F)
+    for c in range(C):
+        disp[c] = [0.5 * (c + 1), 1.0 + c, -0.25 * (c + 1), 0.0]
+        deriv[c] = [0.1, -0.2, 0.05, 0.025]
+        turb[c] = [0.3, 1.7, -0.4][c]
+    pts = np.random.default_rng(3).uniform(-500, 500, (64, 2)).astype(F)
+    for lod in (0.0, 2.5):
+        d, nrm, foam = so.surface(disp, deriv, turb, [100.0, 31.0, 7.0], pts, lod)
+        assert np.allclose(d, [3.0, 6.0, -1.5], atol=1e-6)
+        sx, sz = 0.3 / 1.15, -0.6 / 1.075
+        want = np.array([-sx, 1.0, -sz]) / np.sqrt(sx * sx + 1 + sz * sz)
+        assert np.allclose(nrm, want, atol=1e-6)
+        assert np.allclose(np.linalg.norm(nrm, axis=1), 1.0, atol=1e-6)
+        assert np.allclose(foam, (1 - 0.3) + (1 - 1.0) + (1 - 0.0), atol=1e-6)  # 1 - saturate(x)
+
+
+def test_surface_sums_cascades_at_their_own_wavelength():
+    C, N = 2, 32
+    rng = np.random.default_rng(4)
+    disp = rng.standard_normal((C, N, N, 4)).astype(F)
+    zero = np.zeros_like(disp)
+    wl = [64.0, 10.0]
+    # a point on a texel centre of both cascades: x = (i + 0.5) * wl / N
+    x = F(2.5 * 64.0 / N)          # texel 2 of cascade 0; 2.5*2 = 5 -> u1 = 0.5 -> fx = 15.5 (between 15 and 16)
+    d, _, _ = so.surface(disp, zero, zero, wl, np.array([[x, x]], F), 0.0)
+    c1 = 0.25 * (disp[1, 15, 15] + disp[1, 15, 16] + disp[1, 16, 15] + disp[1, 16, 16])
+    assert np.allclose(d[0], (disp[0, 2, 2] + c1)[:3], atol=1e-5)
+
+
+def test_displaced_heights_invert_a_gerstner_wave():
+    """One trochoidal wave along x: Dx = -A sin(kx), Dy = A cos(kx).  The surface above X is at the q with
+    q - A sin(kq) = X; the fixed-point iteration contracts with ratio A k."""
+    N, wl, A = 256, 64.0, 1.5
+    k = 2 * np.pi / wl * 2  # two periods per tile: A k = 0.29
+    xs = (np.arange(N) + 0.5) * wl / N
+    disp = np.zeros((1, N, N, 4), F)
+    disp[0, :, :, 0] = (-A * np.sin(k * xs))[None, :]
+    disp[0, :, :, 1] = (A * np.cos(k * xs))[None, :]
+    X = np.random.default_rng(5).uniform(0, wl, (500, 2)).astype(F)
+    h, (qx, qz) = so.displaced_heights(disp, [wl], X, iterations=12, return_q=True)
+    # exact inversion by Newton in float64
+    q = X[:, 0].astype(np.float64)
+    for _ in range(50):
+        q -= (q - A * np.sin(k * q) - X[:, 0]) / (1 - A * k * np.cos(k * q))
+    assert np.abs(qx - q).max() < 2e-3            # bilinear interpolation error of the sampled sine
+    assert np.abs(h - A * np.cos(k * q)).max() < 2e-3
+    assert np.array_equal(qz, X[:, 1])            # no z displacement
+    # the un-inverted lookup is visibly wrong, and 4 iterations (the library's setting) are within (A k)^5
+    h0 = so.displaced_heights(disp, [wl], X, iterations=0)
+    assert np.abs(h0 - A * np.cos(k * q)).max() > 0.3
+    h4 = so.displaced_heights(disp, [wl], X, iterations=4)
+    assert np.abs(h4 - A * np.cos(k * q)).max() < A * (A * k) ** 5 * 3 + 2e-3
