@@ -54,8 +54,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // next to the column pass of frame f on the same SMs.  Completion stays transitive along the stream
 // through the counters: a column tile waits for its layer's rows, and a row CTA waits, before its first
 // store, for the previous frame's columns of its layer to be finished and stored.
-__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// (pdl_trigger / pdl_wait live in ocean_tma.cuh)
 
 // Optional per-CTA phase trace (variants/ builds with -DOCEAN_TRACE only; never in the product build):
 // thread 0 of every CTA records %globaltimer / clock64 / %smid at phase boundaries.
@@ -144,6 +143,42 @@ template <int N> struct ColCfg {
     using FFT = LineFFT<N, W, true, DB>;
 };
 
+// sin and cos of a phase: 3-term Cody-Waite reduction to [-pi/4, pi/4] (the constants CUDA's own
+// sincosf uses on its fast path, valid below 105615 rad) followed by the SFU approximations, whose
+// absolute error (~4e-7) is of the order of the transform's own rounding.  Larger phases take the
+// library path.
+__device__ __noinline__ float2 phase_sincos_large(float x) {
+    float sn, cs;
+    sincosf(x, &sn, &cs);
+    return make_float2(sn, cs);
+}
+__device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
+    if (fabsf(x) > 105615.0f) {
+        const float2 r = phase_sincos_large(x);
+        sn = r.x;
+        cs = r.y;
+        return;
+    }
+    const float magic = 12582912.0f;  // 1.5 * 2^23: adding it rounds to the nearest integer
+    const float qf = __fmaf_rn(x, 0.636619772f, magic);
+    const int iq = __float_as_int(qf);  // low bits = round(x * 2/pi)
+    const float q = qf - magic;
+    float r = __fmaf_rn(q, -1.57079601e+00f, x);
+    r = __fmaf_rn(q, -3.13916473e-07f, r);
+    r = __fmaf_rn(q, -5.39030253e-15f, r);
+    const float s0 = __sinf(r), c0 = __cosf(r);
+    const bool odd = iq & 1;
+    const float sv = odd ? c0 : s0, cv = odd ? s0 : c0;
+    sn = __int_as_float(__float_as_int(sv) ^ ((iq & 2) << 30));
+    cs = __int_as_float(__float_as_int(cv) ^ (((iq + 1) & 2) << 30));
+}
+
+// measured on B200 at 4 x 512^2: the SFU path executes 18% fewer instructions but the frame is not
+// issue-bound (27.2 us vs 26.9 us with the library sincosf), so the precise path stays the default
+#ifndef OCEAN_ROWS_FAST_SINCOS
+#define OCEAN_ROWS_FAST_SINCOS 0
+#endif
+
 // ---------------------------------------------------------------------------------------------
 template <int N>
 __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_rows_kernel(const FrameArgs a) {
@@ -190,7 +225,11 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         const float ik = wv.x;
         // TD:23-26
         float sn, cs;
+#if OCEAN_ROWS_FAST_SINCOS
+        phase_sincos(wv.y * time, sn, cs);
+#else
         sincosf(wv.y * time, &sn, &cs);
+#endif
         const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
         const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
         const float ihx = -hy, ihy = hx;
@@ -237,7 +276,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         const size_t first = (size_t)blockIdx.x * R;  // R divides N: all rows of a CTA lie in one layer
         const size_t n = first + R <= totalRows ? R : totalRows - first;
         __threadfence();
+#ifndef OCEAN_ROWS_NO_PROXY_FENCE
         fence_proxy_async_global();
+#endif
         atomicAdd(a.rowsDone + first / N, (unsigned long long)n);
     }
     TRACE(0, blockIdx.x, 7);
@@ -269,29 +310,6 @@ template <int N> struct RowPairCfg {
     static constexpr int TW_BYTES = FFT::TWIDDLE_ENTRIES * 8;
     static constexpr int SMEM_BYTES = 2 * N * 16 + TW_BYTES;
 };
-
-// sin and cos of a phase: 3-term Cody-Waite reduction to [-pi/4, pi/4] (the constants CUDA's own
-// sincosf uses on its fast path, valid below 105615 rad) followed by the SFU approximations, whose
-// absolute error (~4e-7) is of the order of the transform's own rounding.  Larger phases take the
-// library path.
-__device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
-    if (fabsf(x) > 105615.0f) {
-        sincosf(x, &sn, &cs);
-        return;
-    }
-    const float magic = 12582912.0f;  // 1.5 * 2^23: adding it rounds to the nearest integer
-    const float qf = __fmaf_rn(x, 0.636619772f, magic);
-    const int iq = __float_as_int(qf);  // low bits = round(x * 2/pi)
-    const float q = qf - magic;
-    float r = __fmaf_rn(q, -1.57079601e+00f, x);
-    r = __fmaf_rn(q, -3.13916473e-07f, r);
-    r = __fmaf_rn(q, -5.39030253e-15f, r);
-    const float s0 = __sinf(r), c0 = __cosf(r);
-    const bool odd = iq & 1;
-    const float sv = odd ? c0 : s0, cv = odd ? s0 : c0;
-    sn = __int_as_float(__float_as_int(sv) ^ ((iq & 2) << 30));
-    cs = __int_as_float(__float_as_int(cv) ^ (((iq + 1) & 2) << 30));
-}
 
 template <int N>
 __global__ void __launch_bounds__(RowPairCfg<N>::THREADS, RowPairCfg<N>::MINB) ocean_rows_pair_kernel(const FrameArgs a) {
@@ -438,6 +456,10 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     const size_t base = (size_t)blockIdx.y * N * N + x;  // texel (x, 0) of this layer
     pdl_trigger();
     pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
+    if (a.mipsDone) {  // a mip chain of the previous frame may still be reading the arrays written below
+        if (threadIdx.x == 0) spin_until_ge(a.mipsDone, a.mipsTarget);
+        __syncthreads();
+    }
     const float lambda = a.lambda;
     // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
     const float sgn = ((x + tid) & 1) ? -1.0f : 1.0f;
@@ -604,6 +626,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             loadB(tile);
         }
         uint32_t parity = 0;
+        bool mipsIdle = a.mipsDone == nullptr;
         for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
             const int next = tile + gridDim.x;
             mbar_wait(&bars[2], parity);  // displacement staged in bufA
@@ -616,6 +639,10 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
                 load(&maps.a, bufA, &bars[0], next);
             }
             mbar_wait(&bars[3], parity);  // derivatives staged in bufB, turbulence in bufT
+            if (!mipsIdle) {  // a mip chain of the previous frame may still be reading these two arrays
+                spin_until_ge(a.mipsDone, a.mipsTarget);
+                mipsIdle = true;
+            }
             store(&maps.deriv, bufB, tile);
             store(&maps.turb, bufT, tile);
             bulk_commit();

@@ -294,6 +294,8 @@ struct OceanHandle {
     float4 *derivMips = nullptr, *turbMips = nullptr;
     int64_t mipsFrame = -1;  // frame index the chains were built from
     bool autoMips = false;   // rebuild them at the end of every frame, as the reference does
+    unsigned long long* mipsDone = nullptr;  // device counter the chain kernels bump when they stop reading
+    unsigned long long mipsSignals = 0;      // its value once every chain launched so far has finished
     // surface-sample scratch: n x (2 in + 7 out) floats
     float* sBuf = nullptr;
     int sCap = 0;
@@ -394,7 +396,9 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     if (doRows && rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
     if (doCols && !doRows && !rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
     workspace_stamp(ws, N, doRows, doCols, &a);
-    if (which == 0 && frame_fused_available(N, &colsMaps)) {
+    a.mipsDone = mipsDone;  // nullptr until a chain has been built on this ocean
+    a.mipsTarget = mipsSignals;
+    if (which == 0 && !mipsDone && frame_fused_available(N, &colsMaps)) {
         OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
         foamZero = false;
         ++frame;
@@ -419,8 +423,13 @@ int OceanHandle::GenerateMips() {
     const size_t bytes = (size_t)C * mip_texels_per_layer(N) * sizeof(float4);
     if (!derivMips) OCEAN_CUDA(cudaMalloc(&derivMips, bytes));
     if (!turbMips) OCEAN_CUDA(cudaMalloc(&turbMips, bytes));
-    OCEAN_CUDA(launch_mip_chain(deriv, derivMips, N, C, stream));
-    OCEAN_CUDA(launch_mip_chain(turb, turbMips, N, C, stream));
+    if (!mipsDone) {
+        OCEAN_CUDA(cudaMalloc(&mipsDone, sizeof(unsigned long long)));
+        OCEAN_CUDA(cudaMemsetAsync(mipsDone, 0, sizeof(unsigned long long), stream));
+    }
+    unsigned long long signals = 0;
+    OCEAN_CUDA(launch_mip_chains(deriv, derivMips, turb, turbMips, N, C, mipsDone, &signals, stream));
+    mipsSignals += signals;
     mipsFrame = frame;
     return OCEAN_OK;
 }
@@ -561,7 +570,7 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, mipsDone};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {

@@ -79,6 +79,11 @@ struct FrameArgs {
     // next frame may overwrite its rows of the workspace once colsDone[layer] >= colsTarget.
     unsigned long long* colsDone;      // device, one counter per layer
     unsigned long long colsTarget;     // N * (column passes issued before this frame)
+    // Mip chains (WB:191-192) read deriv / turb after a frame without holding the next frame back: the
+    // column pass waits for mipsDone >= mipsTarget before it overwrites those two arrays (nullptr: no chain
+    // was ever built on this ocean).
+    const unsigned long long* mipsDone;
+    unsigned long long mipsTarget;
     // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
     // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
     const void* l2Window;
@@ -116,7 +121,9 @@ inline size_t mip_level_offset(int N, int level) {                            //
     const size_t m = (size_t)(N >> (level - 1));
     return ((size_t)N * N - m * m) / 3;
 }
-cudaError_t launch_mip_chain(const float4* base, float4* mips, int N, int layers, cudaStream_t s);
+// Builds both chains; the last kernel adds *signals to `done` in total (release) when its reads are over.
+cudaError_t launch_mip_chains(const float4* baseA, float4* mipsA, const float4* baseB /*or nullptr*/, float4* mipsB, int N, int layers,
+                              unsigned long long* done, unsigned long long* signals, cudaStream_t s);
 cudaError_t launch_surface(const float4* disp, const float4* deriv, const float4* turb, const float4* derivMips, const float4* turbMips,
                            int N, int C, const float* wavelengths /*host, C*/, const float2* pts, int n, float lod, float* outDisp,
                            float* outNormal, float* outFoam, cudaStream_t s);

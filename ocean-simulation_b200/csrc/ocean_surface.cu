@@ -11,6 +11,7 @@
 // Unity's mip filter is not in the reference tree: the chain is DEFINED here as the 2x2 box filter
 // (parity unpinned for that one step; everything downstream of it is pinned to the oracle).
 #include "ocean_internal.h"
+#include "ocean_tma.cuh"
 
 namespace ocean {
 
@@ -19,17 +20,95 @@ __device__ __forceinline__ float4 f4_lerp(float4 a, float4 b, float t) {
     return make_float4(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t, a.w + (b.w - a.w) * t);
 }
 
-// dst[layer][y][x] = mean of the 2x2 block of src[layer]; src is n x n, dst is n/2 x n/2
-__global__ void ocean_mip_kernel(const float4* __restrict__ src, size_t srcLayerStride, float4* __restrict__ dst,
-                                 size_t dstLayerStride, int n) {
-    const int h = n >> 1;
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= h) return;
-    const float4* s = src + (size_t)blockIdx.z * srcLayerStride + (size_t)(2 * y) * n + 2 * x;
-    const float4 a = s[0], b = s[1], c = s[n], d = s[n + 1];
-    dst[(size_t)blockIdx.z * dstLayerStride + (size_t)y * h + x] =
-        make_float4(((a.x + b.x) + (c.x + d.x)) * 0.25f, ((a.y + b.y) + (c.y + d.y)) * 0.25f,
-                    ((a.z + b.z) + (c.z + d.z)) * 0.25f, ((a.w + b.w) + (c.w + d.w)) * 0.25f);
+// The chain in two launches for both arrays (instead of one launch per level per array):
+//   head: each CTA owns a T0 x T0 block of level 0 (T0 = min(32, N)) of one layer of one array and
+//         reduces it through log2(T0) levels, keeping the running level in shared memory;
+//   tail: one CTA per layer per array finishes the remaining levels (N/T0 squared and smaller).
+// Every output texel is ((a + b) + (c + d)) * 0.25 of the level above, whatever kernel produces it.
+__device__ __forceinline__ float4 box4(float4 a, float4 b, float4 c, float4 d) {
+    return make_float4(((a.x + b.x) + (c.x + d.x)) * 0.25f, ((a.y + b.y) + (c.y + d.y)) * 0.25f,
+                       ((a.z + b.z) + (c.z + d.z)) * 0.25f, ((a.w + b.w) + (c.w + d.w)) * 0.25f);
+}
+
+__host__ __device__ __forceinline__ size_t mip_offset(int N, int level) {
+    // texels of levels 1..level-1 = (N^2 - (N >> (level-1))^2) / 3
+    const size_t n2 = (size_t)N * N, m = (size_t)(N >> (level - 1));
+    return (n2 - m * m) / 3;
+}
+
+struct MipArgs {
+    const float4* base[2];  // level 0 of the two arrays, [layers][N][N]
+    float4* mips[2];        // their chains, [layers][(N*N-1)/3]
+    int N, layers, levels;  // levels = log2(N)
+    unsigned long long* done;  // += 1 per CTA of the LAST kernel of the chain, once it has stopped reading
+};
+
+// The next frame's row pass does not depend on the chain, so both kernels let their successor start at
+// once (pdl_trigger); the column pass that would overwrite the arrays waits for `done` instead.
+__device__ __forceinline__ void mip_signal(unsigned long long* done) {
+    __syncthreads();
+    if (done && threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(done, 1ull);
+    }
+}
+
+template <int T0>
+__global__ void __launch_bounds__((T0 / 2) * (T0 / 2)) ocean_mip_head_kernel(const __grid_constant__ MipArgs a, const bool last) {
+    constexpr int H = T0 / 2;
+    __shared__ float4 cur[H * H];
+    __shared__ float4 nxt[(H / 2) * (H / 2) > 0 ? (H / 2) * (H / 2) : 1];
+    const int N = a.N;
+    pdl_trigger();
+    pdl_wait();  // the column pass that produced level 0 has completed
+    const int arr = blockIdx.z / a.layers, layer = blockIdx.z % a.layers;
+    const float4* src = a.base[arr] + (size_t)layer * N * N;
+    float4* chain = a.mips[arr] + (size_t)layer * (((size_t)N * N - 1) / 3);
+    const int tx = threadIdx.x % H, ty = threadIdx.x / H;
+    {   // level 1 from level 0
+        const int x = blockIdx.x * H + tx, y = blockIdx.y * H + ty, h = N >> 1;
+        const float4* s = src + (size_t)(2 * y) * N + 2 * x;
+        const float4 v = box4(__ldg(s), __ldg(s + 1), __ldg(s + N), __ldg(s + N + 1));
+        chain[(size_t)y * h + x] = v;
+        cur[ty * H + tx] = v;
+    }
+    float4* from = cur;
+    float4* to = nxt;
+    int level = 2;
+    for (int w = H / 2; w >= 1; w >>= 1, ++level) {  // w x w texels of `level` in this CTA
+        __syncthreads();
+        if ((int)threadIdx.x < w * w) {
+            const int lx = threadIdx.x % w, ly = threadIdx.x / w, sw = 2 * w;
+            const float4* s = from + (2 * ly) * sw + 2 * lx;
+            const float4 v = box4(s[0], s[1], s[sw], s[sw + 1]);
+            const int n = N >> level;
+            chain[mip_offset(N, level) + (size_t)(blockIdx.y * w + ly) * n + blockIdx.x * w + lx] = v;
+            to[ly * w + lx] = v;
+        }
+        float4* t = from; from = to; to = t;
+    }
+    if (last) mip_signal(a.done);
+}
+
+// levels first..a.levels of one layer of one array, each from the level above in global memory
+__global__ void __launch_bounds__(1024) ocean_mip_tail_kernel(const __grid_constant__ MipArgs a, int first) {
+    const int N = a.N;
+    pdl_trigger();
+    pdl_wait();  // launched as a programmatic dependent of the head kernel: wait for its levels
+    const int arr = blockIdx.x / a.layers, layer = blockIdx.x % a.layers;
+    float4* chain = a.mips[arr] + (size_t)layer * (((size_t)N * N - 1) / 3);
+    for (int level = first; level <= a.levels; ++level) {
+        const int n = N >> level, sn = 2 * n;
+        const float4* s = chain + mip_offset(N, level - 1);
+        float4* d = chain + mip_offset(N, level);
+        for (int i = threadIdx.x; i < n * n; i += blockDim.x) {
+            const int x = i % n, y = i / n;
+            const float4* p = s + (size_t)(2 * y) * sn + 2 * x;
+            d[i] = box4(__ldcg(p), __ldcg(p + 1), __ldcg(p + sn), __ldcg(p + sn + 1));
+        }
+        __syncthreads();  // the level just written is the next one's source (same CTA)
+    }
+    mip_signal(a.done);
 }
 
 // One array as the sampler sees it: level 0 is the output array itself, levels >= 1 live in a
@@ -38,12 +117,6 @@ struct MipArray {
     const float4* base;  // [C][N][N]
     const float4* mips;  // [C][(N*N-1)/3] or nullptr (no chain: every LOD clamps to level 0)
 };
-
-__device__ __forceinline__ size_t mip_offset(int N, int level) {
-    // (N^2/4) * (1 - 4^-(level-1)) / (3/4)  =  (N^2 - (N >> (level-1))^2) / 3
-    const size_t n2 = (size_t)N * N, m = (size_t)(N >> (level - 1));
-    return (n2 - m * m) / 3;
-}
 
 __device__ __forceinline__ float4 sample_bilinear(const float4* __restrict__ img, int n, float u, float v) {
     // Repeat wrap, texel centres at (i + 0.5)/n
@@ -144,18 +217,41 @@ __global__ void ocean_displaced_query_kernel(const __grid_constant__ DisplacedQu
     a.out[i] = height;
 }
 
-cudaError_t launch_mip_chain(const float4* base, float4* mips, int N, int layers, cudaStream_t s) {
-    const size_t perLayer = ((size_t)N * N - 1) / 3;
-    const float4* src = base;
-    size_t srcStride = (size_t)N * N;
-    for (int level = 1, n = N; n > 1; ++level, n >>= 1) {
-        float4* dst = mips + ((size_t)N * N - (size_t)n * n) / 3;  // = mip_offset(N, level)
-        const int h = n >> 1;
-        dim3 block(h < 128 ? h : 128), grid((h + block.x - 1) / block.x, h, layers);
-        ocean_mip_kernel<<<grid, block, 0, s>>>(src, srcStride, dst, perLayer, n);
+cudaError_t launch_mip_chains(const float4* baseA, float4* mipsA, const float4* baseB, float4* mipsB, int N, int layers,
+                              unsigned long long* done, unsigned long long* signals, cudaStream_t s) {
+    MipArgs a;
+    a.base[0] = baseA; a.mips[0] = mipsA; a.base[1] = baseB; a.mips[1] = mipsB;
+    a.N = N; a.layers = layers; a.levels = 0; a.done = done;
+    while ((N >> a.levels) > 1) ++a.levels;
+    const int arrays = baseB ? 2 : 1;
+    const int headLevels = N >= 32 ? 5 : 4;
+    const bool headIsLast = a.levels <= headLevels;
+    // both kernels are programmatic dependents: they are scheduled while their predecessor drains and
+    // wait for its completion themselves (griddepcontrol.wait)
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    dim3 grid(N >= 32 ? N / 32 : 1, N >= 32 ? N / 32 : 1, arrays * layers);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid; cfg.blockDim = dim3(N >= 32 ? 256 : 64); cfg.stream = s;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaError_t e = N >= 32 ? cudaLaunchKernelEx(&cfg, ocean_mip_head_kernel<32>, a, headIsLast)
+                                : cudaLaunchKernelEx(&cfg, ocean_mip_head_kernel<16>, a, headIsLast);  // N = 16 (OCEAN_MIN_SIZE)
         count_launch();
-        src = dst;
-        srcStride = perLayer;
+        if (e != cudaSuccess) return e;
+    }
+    if (signals) *signals = headIsLast ? (unsigned long long)grid.x * grid.y * grid.z : (unsigned long long)(arrays * layers);
+    if (!headIsLast) {
+        const int side = N >> (headLevels + 1);
+        int threads = side * side;
+        threads = threads < 32 ? 32 : (threads > 1024 ? 1024 : threads);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(arrays * layers); cfg.blockDim = dim3(threads); cfg.stream = s;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, ocean_mip_tail_kernel, a, headLevels + 1);
+        count_launch();
+        if (e != cudaSuccess) return e;
     }
     return cudaGetLastError();
 }

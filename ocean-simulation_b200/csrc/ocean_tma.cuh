@@ -7,6 +7,12 @@
 
 namespace ocean {
 
+// Programmatic dependent launch: pdl_trigger() lets the next kernel in the stream (if it was launched with
+// the programmatic-stream-serialization attribute) start; pdl_wait() blocks until every predecessor grid
+// has completed and its writes are visible.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t arrivals) {

@@ -7,11 +7,8 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "rb7": ["-DOCEAN_ROWS512_MAXB=7"],
-    "rb8": ["-DOCEAN_ROWS512_MAXB=8"],
-    "rb10": ["-DOCEAN_ROWS512_MAXB=10"],
-    "rb7_m7": ["-DOCEAN_ROWS512_MAXB=7", "-DOCEAN_ROWS512_MINB=7"],
-    "rb5_m7": ["-DOCEAN_ROWS512_MAXB=5", "-DOCEAN_ROWS512_MINB=7"],
+    "fastsin": ["-DOCEAN_ROWS_FAST_SINCOS=1"],
+    "nopf": ["-DOCEAN_ROWS_NO_PROXY_FENCE"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
@@ -23,7 +20,7 @@ if __name__ == "__main__":
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
         info = re.findall(r"ocean_(rows|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
-        others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o")]
+        others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o", "ocean_surface.o")]
         subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", os.path.join(HERE, "lib_%s.so" % n), obj] + others)
         os.remove(obj)
         print(n, info, flush=True)
