@@ -124,6 +124,26 @@ struct Epilogue {
     }
 };
 
+// Ensemble checksums fused into the column pass: 64-bit sums of the fp32 bit patterns of a state's three
+// output arrays (integer addition: order-independent, so identical to a separate reduction pass).
+__device__ __forceinline__ unsigned long long bits_sum(const float4 v) {
+    return (unsigned long long)__float_as_uint(v.x) + __float_as_uint(v.y) + __float_as_uint(v.z) + __float_as_uint(v.w);
+}
+__device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned long long sd, unsigned long long sv,
+                                               unsigned long long st) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sd += __shfl_xor_sync(0xffffffffu, sd, o);
+        sv += __shfl_xor_sync(0xffffffffu, sv, o);
+        st += __shfl_xor_sync(0xffffffffu, st, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out + 0, sd);
+        atomicAdd(out + 1, sv);
+        atomicAdd(out + 2, st);
+    }
+}
+
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
@@ -473,10 +493,15 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
         for (int j = 0; j < 8; ++j) r[j] = c2_from(__ldcg(in + (size_t)(tid + T * j) * N));
     }
     FFT::run(r, smem, tid, xw, a.twiddle, 0);
+    unsigned long long sumD = 0, sumV = 0, sumT = 0;
     {
         float4* __restrict__ disp = a.disp + base;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) st_stream(disp + (size_t)(tid + T * j) * N, ep.displacement(r[j], dxz[j]));
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = ep.displacement(r[j], dxz[j]);
+            st_stream(disp + (size_t)(tid + T * j) * N, v);
+            if (a.checksums) sumD += bits_sum(v);
+        }
     }
     {
         const float4* __restrict__ in = a.rowsB + base;
@@ -493,14 +518,20 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
         for (int j = 0; j < 8; ++j) {
             const size_t o = (size_t)(tid + T * j) * N;
             float jac;
-            st_stream(deriv + o, ep.derivatives(r[j], dxz[j], jac));
+            const float4 dv = ep.derivatives(r[j], dxz[j], jac);
+            st_stream(deriv + o, dv);
             // RF:28-32
             float foam = zeroFoam ? 0.0f : ld_stream(turb + o).x;
             foam *= decay;
             if (foam < jac) foam += jac;
             st_stream(turb + o, make_float4(foam, foam, foam, foam));
+            if (a.checksums) {
+                sumV += bits_sum(dv);
+                sumT += 4ull * __float_as_uint(foam);
+            }
         }
     }
+    if (a.checksums) checksum_flush(a.checksums + (size_t)(blockIdx.y / a.C) * 3, sumD, sumV, sumT);
     // hand the layer's workspace rows back to the next frame's row pass
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -550,7 +581,9 @@ template <int N> struct ColTmaCfg {
     static constexpr int SMEM_BYTES = 3 * TILE_ELEMS * 16 + TW_BYTES + 64;  // A, B, turbulence staging, twiddles, mbarriers
 };
 
-template <int N>
+// CK: also reduce the ensemble checksums (FrameArgs::checksums) -- per-warp partial sums travel to the
+// producer lane through shared memory under the `staged B` barrier, one set of atomics per tile.
+template <int N, bool CK = false>
 __global__ void __launch_bounds__(ColTmaCfg<N>::THREADS, ColTmaCfg<N>::MINB)
 ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs a, const int totalTiles) {
     using Cfg = ColTmaCfg<N>;
@@ -562,6 +595,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     float4* bufT = smem + 2 * Cfg::TILE_ELEMS;
     float2* twS = (float2*)(smem + 3 * Cfg::TILE_ELEMS);
     uint64_t* bars = (uint64_t*)((char*)twS + Cfg::TW_BYTES);  // [0] full A, [1] full B, [2] staged A, [3] staged B
+    __shared__ unsigned long long ckPart[CK ? (Cfg::COMPUTE / 32) * 3 : 1];  // per-warp (disp, deriv, turb) sums of a tile
 
     pdl_trigger();
     TRACE(1, blockIdx.x, 0);
@@ -643,6 +677,19 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
                 spin_until_ge(a.mipsDone, a.mipsTarget);
                 mipsIdle = true;
             }
+            if constexpr (CK) {
+                unsigned long long sd = 0, sv = 0, st = 0;
+#pragma unroll
+                for (int w = 0; w < Cfg::COMPUTE / 32; ++w) {
+                    sd += ckPart[w * 3 + 0];
+                    sv += ckPart[w * 3 + 1];
+                    st += ckPart[w * 3 + 2];
+                }
+                unsigned long long* out = a.checksums + (size_t)((tile / TILES_PER_LAYER) / a.C) * 3;
+                atomicAdd(out + 0, sd);
+                atomicAdd(out + 1, sv);
+                atomicAdd(out + 2, st);
+            }
             store(&maps.deriv, bufB, tile);
             store(&maps.turb, bufT, tile);
             bulk_commit();
@@ -680,8 +727,13 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         FFT::run(r, bufA, tid, xw, twS, 0);
         FFT::barrier();  // every thread has finished reading the last exchange
         TRACE(1, tile, 3);
+        unsigned long long sumD = 0, sumV = 0, sumT = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) bufA[(tid + T * j) * W + xw] = ep.displacement(r[j], dxz[j]);
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = ep.displacement(r[j], dxz[j]);
+            bufA[(tid + T * j) * W + xw] = v;
+            if constexpr (CK) sumD += bits_sum(v);
+        }
         fence_proxy_async();
         mbar_arrive(&bars[2]);
         TRACE(1, tile, 4);
@@ -698,13 +750,30 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         for (int j = 0; j < 8; ++j) {
             const int o = (tid + T * j) * W + xw;
             float jac;
-            bufB[o] = ep.derivatives(r[j], dxz[j], jac);                             // RF:26-27
+            const float4 dv = ep.derivatives(r[j], dxz[j], jac);                     // RF:26-27
+            bufB[o] = dv;
             float f = zeroFoam ? 0.0f : bufT[o].x * decay;                           // RF:28-30 (incoming texel, TMA-staged)
             if (f < jac) f += jac;                                                   // RF:31
             bufT[o] = make_float4(f, f, f, f);                                       // RF:32
+            if constexpr (CK) {
+                sumV += bits_sum(dv);
+                sumT += 4ull * __float_as_uint(f);
+            }
+        }
+        if constexpr (CK) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                sumD += __shfl_xor_sync(0xffffffffu, sumD, o);
+                sumV += __shfl_xor_sync(0xffffffffu, sumV, o);
+                sumT += __shfl_xor_sync(0xffffffffu, sumT, o);
+            }
+            if ((threadIdx.x & 31) == 0) {
+                unsigned long long* part = ckPart + (threadIdx.x >> 5) * 3;
+                part[0] = sumD; part[1] = sumV; part[2] = sumT;
+            }
         }
         fence_proxy_async();
-        mbar_arrive(&bars[3]);
+        mbar_arrive(&bars[3]);  // (release: the producer lane reads ckPart after its wait on this barrier)
         TRACE(1, tile, 7);
     }
     TRACE(1, blockIdx.x, 8);
@@ -862,19 +931,25 @@ template <int N> static cudaError_t cols_tma_launch(const FrameArgs& a, const Co
     const int totalTiles = a.layers * (N / Cfg::W);
     static int ctasPerSM = 0;  // resident CTAs per SM for this kernel: the persistent grid size
     if (ctasPerSM == 0) {
-        int n = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_cols_tma_kernel<N>, Cfg::THREADS, Cfg::SMEM_BYTES);
+        int n = 0, nck = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_cols_tma_kernel<N, false>, Cfg::THREADS, Cfg::SMEM_BYTES);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nck, ocean_cols_tma_kernel<N, true>, Cfg::THREADS, Cfg::SMEM_BYTES);
+        if (nck < n) n = nck;
         ctasPerSM = n > 0 ? n : 1;
         if (ctasPerSM > OCEAN_COLS_TMA_CTAS_PER_SM) ctasPerSM = OCEAN_COLS_TMA_CTAS_PER_SM;
     }
     const int slots = num_sms() * ctasPerSM;
     const int grid = totalTiles < slots ? totalTiles : slots;
-    return launch_pdl(true, a, ocean_cols_tma_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
+    if (a.checksums) return launch_pdl(true, a, ocean_cols_tma_kernel<N, true>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
+    return launch_pdl(true, a, ocean_cols_tma_kernel<N, false>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a, totalTiles);
 }
 template <int N> static cudaError_t configure_tma() {
-    cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    cudaFuncSetAttribute(ocean_cols_tma_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    e = cudaFuncSetAttribute(ocean_cols_tma_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ColTmaCfg<N>::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    cudaFuncSetAttribute(ocean_cols_tma_kernel<N, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(ocean_cols_tma_kernel<N, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     return cudaSuccess;
 }
 template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsTmaMaps& m, cudaStream_t s, bool early) {
@@ -999,15 +1074,21 @@ extern "C" int ocean_debug_trace_copy(unsigned long long* times, unsigned* smids
 }
 #endif
 
+// true when the row pass in use reads FrameArgs::h0c (the pair-row kernel): only then is it allocated and filled
+bool rows_need_h0c() {
+#ifdef OCEAN_ROWS_USE_PAIR
+    return true;
+#else
+    static const bool pair = getenv("OCEAN_ROWS_PAIR") != nullptr;
+    return pair;
+#endif
+}
+
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early) {
     // The pair-row kernel moves half the bytes and issues fewer instructions, but on B200 at N = 512 the
     // one-row kernel is still ~1 us/frame faster (more, smaller CTAs hide more latency): it stays the
     // default until the pair kernel wins.  OCEAN_ROWS_PAIR=1 (or -DOCEAN_ROWS_USE_PAIR) selects it.
-#ifdef OCEAN_ROWS_USE_PAIR
-    const bool legacy = false;
-#else
-    static const bool legacy = getenv("OCEAN_ROWS_PAIR") == nullptr;
-#endif
+    const bool legacy = !rows_need_h0c() || a.h0c == nullptr;
     if (!legacy) {
         if (a.N == 256) return rows_pair_launch<256>(a, s, early);
         if (a.N == 512) return rows_pair_launch<512>(a, s, early);

@@ -337,7 +337,7 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
     OCEAN_CUDA(cudaMalloc(&h0, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&wave, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&waveHot, C * t * sizeof(float2)));
-    OCEAN_CUDA(cudaMalloc(&h0c, C * t * sizeof(float2)));
+    if (rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&h0c, C * t * sizeof(float2)));
     OCEAN_CUDA(cudaMalloc(&disp, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&deriv, C * t * sizeof(float4)));
     OCEAN_CUDA(cudaMalloc(&turb, C * t * sizeof(float4)));
@@ -622,7 +622,7 @@ int OceanEnsemble::create() {
     rowsA = ws->planeA();
     rowsB = ws->planeB();
     OCEAN_CUDA(cudaMalloc(&waveHot, (size_t)batch * C * t * sizeof(float2)));
-    OCEAN_CUDA(cudaMalloc(&h0c, (size_t)batch * C * t * sizeof(float2)));
+    if (rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&h0c, (size_t)batch * C * t * sizeof(float2)));
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
@@ -691,13 +691,14 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         l2_window(device, ws, &fa);
         if (frame_fused_available(N, &colsMaps)) {
             OCEAN_CUDA(launch_frame(fa, &colsMaps, stream, false));  // follows the init kernel: no early start
+            OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
+            OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
+            OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));
         } else {
+            fa.checksums = sumDev[b];  // reduced inside the column pass: the outputs are not read back
             OCEAN_CUDA(launch_rows(fa, stream, false));
             OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
         }
-        OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
-        OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
-        OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));
         OCEAN_CUDA(cudaMemcpyAsync(sumHost[b], sumDev[b], (size_t)nb * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
         OCEAN_CUDA(cudaEventRecord(done[b], stream));
         pendingBase[b] = base; pendingCount[b] = nb;

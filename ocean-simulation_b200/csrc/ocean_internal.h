@@ -84,6 +84,9 @@ struct FrameArgs {
     // was ever built on this ocean).
     const unsigned long long* mipsDone;
     unsigned long long mipsTarget;
+    // Ensembles: when not nullptr the column pass adds, per state (= layer / C), the 64-bit sums of the fp32
+    // bit patterns of the texels it produces to checksums[state * 3 + {0: disp, 1: deriv, 2: turb}].
+    unsigned long long* checksums;
     // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
     // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
     const void* l2Window;
@@ -112,6 +115,7 @@ cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early);
 cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s);
 // The whole frame as one persistent kernel (ocean_fused.cuh), where available (N = 256, 512).
 bool frame_fused_available(int N, const ColsTmaMaps* maps);
+bool rows_need_h0c();  // the selected row pass reads FrameArgs::h0c / InitArgs::h0c (else they stay nullptr)
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
