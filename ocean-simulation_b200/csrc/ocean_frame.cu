@@ -572,7 +572,7 @@ template <int N> struct ColTmaCfg {
     static constexpr int W = OCEAN_COLS_TMA_W;
     static constexpr int COMPUTE = W * T;                      // compute threads
     static constexpr int THREADS = COMPUTE + 32;               // + producer warp
-    static constexpr int MINB = OCEAN_COLS_TMA_MINB;
+    static constexpr int MINB = N >= 1024 ? 1 : OCEAN_COLS_TMA_MINB;  // N = 1024: 3 x 64 KiB tiles, one CTA per SM
     static constexpr int BOX_ROWS = N < 256 ? N : 256;
     static constexpr int NBOX = N / BOX_ROWS;
     static constexpr int TILE_ELEMS = N * W;                    // 128-bit elements per tile plane
@@ -972,7 +972,7 @@ template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsT
     const int grid = totalItems < slots ? totalItems : slots;
     return launch_pdl(early, a, ocean_frame_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a);
 }
-static bool tma_size(int N) { return N == 256 || N == 512; }
+static bool tma_size(int N) { return N == 256 || N == 512 || N == 1024; }
 // Opt-in (OCEAN_FUSED=1 or -DOCEAN_USE_FUSED): measured 29.3 us/frame against 26.9 us for the
 // two-kernel path at 4 x 512^2 -- its items still wait for their just-in-time loads.
 bool frame_fused_available(int N, const ColsTmaMaps* maps) {
@@ -981,7 +981,7 @@ bool frame_fused_available(int N, const ColsTmaMaps* maps) {
 #else
     static const bool on = getenv("OCEAN_FUSED") != nullptr;
 #endif
-    return on && tma_size(N) && maps && maps->valid;
+    return on && (N == 256 || N == 512) && maps && maps->valid;
 }
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early) {
     if (a.N == 512) return frame_launch<512>(a, *maps, s, early);
@@ -1036,8 +1036,8 @@ template <int N> static cudaError_t configure() {
 }
 template <int N> static const char* describe() {
     static char buf[512];
-    if (N == 512 || N == 256) {
-        constexpr int M = (N == 512 || N == 256) ? N : 512;
+    if (N == 1024 || N == 512 || N == 256) {
+        constexpr int M = (N == 1024 || N == 512 || N == 256) ? N : 512;
         snprintf(buf, sizeof buf,
                  "rows<N=%d>: %d rows/CTA, %d threads, %d B smem (cp.async-staged row = exchange buffer); "
                  "cols_tma<N=%d>: persistent warp-specialised, %d columns/tile, %d threads, %d B smem (TMA in, TMA out)",
@@ -1104,6 +1104,7 @@ cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_
     if (maps && maps->valid) {
         if (a.N == 512) return cols_tma_launch<512>(a, *maps, s);
         if (a.N == 256) return cols_tma_launch<256>(a, *maps, s);
+        if (a.N == 1024) return cols_tma_launch<1024>(a, *maps, s);
     }
 #define CALL(n) cols_launch<n>(a, s)
     OCEAN_DISPATCH_N(a.N, CALL)
@@ -1117,6 +1118,7 @@ cudaError_t configure_frame_kernels(int N) {
     if (N == 2048) { cudaError_t e = configure_pair<2048>(); if (e != cudaSuccess) return e; }
     if (N == 512) { cudaError_t e = configure_tma<512>(); if (e != cudaSuccess) return e; }
     if (N == 256) { cudaError_t e = configure_tma<256>(); if (e != cudaSuccess) return e; }
+    if (N == 1024) { cudaError_t e = configure_tma<1024>(); if (e != cudaSuccess) return e; }
 #define CALL(n) configure<n>()
     OCEAN_DISPATCH_N(N, CALL)
 #undef CALL
