@@ -212,6 +212,82 @@ struct LineFFT {
         }
     }
 
+    // Two transforms of the same line geometry advanced stage by stage together (single buffer only): each
+    // twiddle is fetched once for both, and the two independent butterfly sets give the scheduler twice the
+    // instruction-level parallelism.  The exchanges still go through the one buffer, a after b.
+    template <int s>
+    __device__ static __forceinline__ void exchange(C2 (&reg)[8], float4* __restrict__ buf, const int tid, const int ln) {
+        constexpr int Cs = 1 << (3 * s);
+        constexpr int Ms = N / Cs;
+        constexpr int Mn = Ms / 8;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) c2_store(&buf[phys<s>(tid + T * q, ln)], reg[q]);
+        barrier();
+        constexpr int rn = (s + 1 == S - 1) ? RLAST : 8;
+        if constexpr (rn == 8) {
+            constexpr int Q = Mn / 8;  // threads per sub-problem in the next stage
+            const int cn = tid / Q, tn = tid & (Q - 1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) reg[j] = c2_load(&buf[phys<s>((cn * 8 + j) * Q + tn, ln)]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8 / rn; ++i)
+#pragma unroll
+                for (int j = 0; j < rn; ++j) reg[i * rn + j] = c2_load(&buf[phys<s>((tid + T * i) * rn + j, ln)]);
+        }
+    }
+    __device__ static __forceinline__ void last_small(C2 (&reg)[8]) {
+        C2 o[8];
+        if constexpr (RLAST == 4) {
+            radix4_inv(reg[0], reg[1], reg[2], reg[3], o[0], o[2], o[4], o[6]);
+            radix4_inv(reg[4], reg[5], reg[6], reg[7], o[1], o[3], o[5], o[7]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                o[i] = reg[2 * i] + reg[2 * i + 1];
+                o[i + 4] = reg[2 * i] - reg[2 * i + 1];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) reg[j] = o[j];
+    }
+    template <int s>
+    __device__ static __forceinline__ void stage2(C2 (&ra)[8], C2 (&rb)[8], float4* __restrict__ smem, const int tid,
+                                                  const int ln, const float2* __restrict__ tw, const int prior) {
+        static_assert(!DOUBLE_BUF, "run2 exchanges through a single buffer");
+        constexpr int Cs = 1 << (3 * s);
+        constexpr int Ms = N / Cs;
+        constexpr bool last = (s == S - 1);
+        if constexpr (!last || RLAST == 8) {
+            radix8_inv(ra);
+            radix8_inv(rb);
+            if constexpr (Ms > 8) {
+#pragma unroll
+                for (int q = 1; q < 8; ++q) {
+                    const float2 w = twiddle(tw, (s * 7 + q - 1) * T + tid);
+                    ra[q] = cmul(ra[q], w);
+                    rb[q] = cmul(rb[q], w);
+                }
+            }
+            if constexpr (!last) {
+                if (prior + s > 0) barrier();  // previous exchange fully read
+                exchange<s>(ra, smem, tid, ln);
+                barrier();
+                exchange<s>(rb, smem, tid, ln);
+            }
+        } else {
+            last_small(ra);
+            last_small(rb);
+        }
+    }
+    __device__ static __forceinline__ void run2(C2 (&ra)[8], C2 (&rb)[8], float4* __restrict__ smem, const int tid,
+                                                const int ln, const float2* __restrict__ tw, const int prior) {
+        stage2<0>(ra, rb, smem, tid, ln, tw, prior);
+        if constexpr (S > 1) stage2<1>(ra, rb, smem, tid, ln, tw, prior);
+        if constexpr (S > 2) stage2<2>(ra, rb, smem, tid, ln, tw, prior);
+        if constexpr (S > 3) stage2<3>(ra, rb, smem, tid, ln, tw, prior);
+    }
+
     // reg[j] = point (tid + T*j) of line `ln` on entry and on return.
     // prior = number of exchanges this CTA has already performed (EXCHANGES per earlier transform).
     // Double buffer: exchange e uses buffer e & 1, one barrier each.  Single buffer: a leading

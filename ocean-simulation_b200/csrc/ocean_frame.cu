@@ -25,6 +25,12 @@ namespace ocean {
 // Streaming (read-once / write-once) accesses keep the intermediate resident in L2.
 __device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
+// read-once 8-byte load that does not allocate in L1 (the twiddle table should own what L1 is left)
+__device__ __forceinline__ float2 ld_once(const float2* p) {
+    float2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+}
 
 // Ampere-style asynchronous copies (LDGSTS): global -> shared without a register round trip, so a
 // thread can have its whole row in flight while holding no data registers.
@@ -144,6 +150,9 @@ __device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned
     }
 }
 
+#ifndef OCEAN_ROWS_WAVE_REGS
+#define OCEAN_ROWS_WAVE_REGS 1
+#endif
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
@@ -151,7 +160,11 @@ template <int N> struct RowCfg {
     static constexpr int MINB = (N == 512) ? OCEAN_ROWS512_MINB : 1;
     // the staged h0 row doubles as the (single) exchange buffer; every exchange is swizzled
     using FFT = LineFFT<N, R, false, false, false>;
+#if OCEAN_ROWS_WAVE_REGS
+    static constexpr int SMEM_BYTES = R * N * 16;        // h0 float4 per texel; (1/|k|, omega) travels in registers
+#else
     static constexpr int SMEM_BYTES = R * N * (16 + 8);  // h0 float4 + (1/|k|, omega) float2 per texel
+#endif
 };
 
 template <int N> struct ColCfg {
@@ -195,6 +208,9 @@ __device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
 
 // measured on B200 at 4 x 512^2: the SFU path executes 18% fewer instructions but the frame is not
 // issue-bound (27.2 us vs 26.9 us with the library sincosf), so the precise path stays the default
+#ifndef OCEAN_ROWS_DUAL_FFT
+#define OCEAN_ROWS_DUAL_FFT 0
+#endif
 #ifndef OCEAN_ROWS_FAST_SINCOS
 #define OCEAN_ROWS_FAST_SINCOS 0
 #endif
@@ -222,12 +238,22 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     // Stage the whole row: 16 asynchronous copies per thread are in flight before any arithmetic.
     // Element x lands in the slot exchange 0 will later use for it, and thread `tid` only ever
     // touches its own 8 elements (x = tid + T*j), so no barrier is needed around the staging.
+#if OCEAN_ROWS_WAVE_REGS
+    float2 wreg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int x = tid + T * j;
+        cp_async16(&hs[FFT::template phys<0>(x, row)], H + x);
+        wreg[j] = ld_once(Wd + x);
+    }
+#else
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int x = tid + T * j;
         cp_async16(&hs[FFT::template phys<0>(x, row)], H + x);
         cp_async8(&ws[row * N + x], Wd + x);
     }
+#endif
     const int layer = (int)(line / N), y = (int)(line & (N - 1));
     const float dk = a.dk[layer % a.C];
     const float kz = (float)(y - N / 2) * dk;  // IS:111 (waveData.z)
@@ -240,7 +266,11 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     for (int j = 0; j < 8; ++j) {
         const int x = tid + T * j;
         const float4 h0 = hs[FFT::template phys<0>(x, row)];
+#if OCEAN_ROWS_WAVE_REGS
+        const float2 wv = wreg[j];
+#else
         const float2 wv = ws[row * N + x];
+#endif
         const float kx = (float)(x - N / 2) * dk;  // IS:111 (waveData.x)
         const float ik = wv.x;
         // TD:23-26
@@ -269,6 +299,26 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     }
 
     TRACE(0, blockIdx.x, 2);
+#if OCEAN_ROWS_DUAL_FFT
+    FFT::run2(pa, pb, smem, tid, row, a.twiddle, 0);
+    TRACE(0, blockIdx.x, 3);
+    // h0 / waveHot are never written by a frame kernel, so everything above may overlap the previous
+    // frame's column pass; the workspace rows it may still be reading can only be overwritten once it
+    // has finished this layer.
+    if (threadIdx.x == 0) spin_until_ge(a.colsDone + (size_t)blockIdx.x * R / N, a.colsTarget);
+    __syncthreads();
+    TRACE(0, blockIdx.x, 4);
+    if (active) {
+        float4* __restrict__ outA = a.rowsA + line * N;
+        float4* __restrict__ outB = a.rowsB + line * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&outA[tid + T * j], pa[j]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&outB[tid + T * j], pb[j]);
+    }
+    TRACE(0, blockIdx.x, 5);
+    TRACE(0, blockIdx.x, 6);
+#else
     FFT::run(pa, smem, tid, row, a.twiddle, 0);
     TRACE(0, blockIdx.x, 3);
     // h0 / waveHot are never written by a frame kernel, so everything above may overlap the previous
@@ -290,13 +340,17 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
 #pragma unroll
         for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
     }
+#endif
     // publish: this CTA's rows of both planes are in memory (visible to the TMA loads of the column pass)
     __syncthreads();
     if (threadIdx.x == 0) {
         const size_t first = (size_t)blockIdx.x * R;  // R divides N: all rows of a CTA lie in one layer
         const size_t n = first + R <= totalRows ? R : totalRows - first;
         __threadfence();
-#ifndef OCEAN_ROWS_NO_PROXY_FENCE
+#ifdef OCEAN_ROWS_PROXY_FENCE
+        // (not needed: the column pass's producer lane executes fence.proxy.async after it acquires the
+        // counter, which already puts a proxy fence on the causality chain  generic st -> release ->
+        // acquire -> fence.proxy.async -> TMA load; FENCE.VIEW.ASYNC here cost 7% of the kernel's warp time)
         fence_proxy_async_global();
 #endif
         atomicAdd(a.rowsDone + first / N, (unsigned long long)n);

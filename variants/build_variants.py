@@ -7,8 +7,7 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "fastsin": ["-DOCEAN_ROWS_FAST_SINCOS=1"],
-    "nopf": ["-DOCEAN_ROWS_NO_PROXY_FENCE"],
+    "wsmem": ["-DOCEAN_ROWS_WAVE_REGS=0"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
