@@ -530,8 +530,8 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     const size_t base = (size_t)blockIdx.y * N * N + x;  // texel (x, 0) of this layer
     pdl_trigger();
     pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
-    if (a.mipsDone) {  // a mip chain of the previous frame may still be reading the arrays written below
-        if (threadIdx.x == 0) spin_until_ge(a.mipsDone, a.mipsTarget);
+    if (a.auxDone) {  // readers of the previous frame's outputs (mip chain, host pack) may still be at work
+        if (threadIdx.x == 0) spin_until_ge(a.auxDone, a.auxTarget);
         __syncthreads();
     }
     const float lambda = a.lambda;
@@ -550,10 +550,12 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     unsigned long long sumD = 0, sumV = 0, sumT = 0;
     {
         float4* __restrict__ disp = a.disp + base;
+        const bool heights = a.heightOut != nullptr && blockIdx.y == 0;  // the readback plane of WB:288 (.g only)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float4 v = ep.displacement(r[j], dxz[j]);
             st_stream(disp + (size_t)(tid + T * j) * N, v);
+            if (heights) a.heightOut[(size_t)(tid + T * j) * N + x] = v.y;
             if (a.checksums) sumD += bits_sum(v);
         }
     }
@@ -714,10 +716,14 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             loadB(tile);
         }
         uint32_t parity = 0;
-        bool mipsIdle = a.mipsDone == nullptr;
+        bool auxIdle = a.auxDone == nullptr;
         for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
             const int next = tile + gridDim.x;
             mbar_wait(&bars[2], parity);  // displacement staged in bufA
+            if (!auxIdle) {  // readers of the previous frame's outputs (mip chain, host pack) may still be at work
+                spin_until_ge(a.auxDone, a.auxTarget);
+                auxIdle = true;
+            }
             store(&maps.disp, bufA, tile);
             bulk_commit();
             bulk_wait_read_all();
@@ -727,10 +733,6 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
                 load(&maps.a, bufA, &bars[0], next);
             }
             mbar_wait(&bars[3], parity);  // derivatives staged in bufB, turbulence in bufT
-            if (!mipsIdle) {  // a mip chain of the previous frame may still be reading these two arrays
-                spin_until_ge(a.mipsDone, a.mipsTarget);
-                mipsIdle = true;
-            }
             if constexpr (CK) {
                 unsigned long long sd = 0, sv = 0, st = 0;
 #pragma unroll
@@ -782,10 +784,12 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         FFT::barrier();  // every thread has finished reading the last exchange
         TRACE(1, tile, 3);
         unsigned long long sumD = 0, sumV = 0, sumT = 0;
+        const bool heights = a.heightOut != nullptr && layer == 0;  // the readback plane of WB:288 (.g only)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float4 v = ep.displacement(r[j], dxz[j]);
             bufA[(tid + T * j) * W + xw] = v;
+            if (heights) a.heightOut[(size_t)(tid + T * j) * N + x] = v.y;
             if constexpr (CK) sumD += bits_sum(v);
         }
         fence_proxy_async();

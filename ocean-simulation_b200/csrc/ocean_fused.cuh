@@ -26,7 +26,7 @@
 
 template <int N> struct FusedCfg {
     static constexpr int T = N / 8;
-    static constexpr int W = 4;                                 // lines (rows or columns) per item
+    static constexpr int W = OCEAN_COLS_TMA_W;                  // lines (rows or columns) per item
     static constexpr int COMPUTE = W * T;
     static constexpr int THREADS = COMPUTE + 32;
     static constexpr int BOX_ROWS = N < 256 ? N : 256;

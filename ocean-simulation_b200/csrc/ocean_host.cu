@@ -245,6 +245,30 @@ static void l2_window(int device, const Workspace* w, FrameArgs* a) {
     a->l2HitRatio = aside >= bytes ? 1.0f : (float)((double)aside / (double)bytes);
 }
 
+// cuStreamWaitValue64 through the runtime's driver entry point (the library links only the CUDA runtime)
+typedef int (*StreamWaitValue64Fn)(cudaStream_t, unsigned long long /*CUdeviceptr*/, unsigned long long, unsigned int);
+static StreamWaitValue64Fn stream_wait_value_fn() {
+    static StreamWaitValue64Fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (!getenv("OCEAN_NO_STREAM_WAIT_VALUE") &&
+            cudaGetDriverEntryPoint("cuStreamWaitValue64", &p, cudaEnableDefault, &q) == cudaSuccess && p &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (StreamWaitValue64Fn)p;
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+static bool stream_wait_value_available() { return stream_wait_value_fn() != nullptr; }
+static cudaError_t stream_wait_value_geq(cudaStream_t s, const unsigned long long* devAddr, unsigned long long value) {
+    const int r = stream_wait_value_fn()(s, (unsigned long long)(uintptr_t)devAddr, value, 0x0u /*CU_STREAM_WAIT_VALUE_GEQ*/);
+    return r == 0 ? cudaSuccess : cudaErrorUnknown;
+}
+
 }  // namespace ocean
 
 using namespace ocean;
@@ -286,6 +310,10 @@ struct OceanHandle {
     int rbSlotMode[RB] = {0, 0, 0};               // layout of each slot's host copy
     bool rbPending[RB] = {false, false, false};
     int rbLatest = -1;  // slot of the newest completed readback
+    // HEIGHT mode: the column pass itself writes the height plane of layer 0 into the slot's staging buffer;
+    // the copy stream waits (stream memory operation) for the layer-0 column counter and ships it -- the
+    // compute stream carries nothing but the two frame kernels
+    bool SlotDone(int i, bool wait);
     // query scratch
     float2* qPts = nullptr;
     float* qOut = nullptr;
@@ -294,8 +322,9 @@ struct OceanHandle {
     float4 *derivMips = nullptr, *turbMips = nullptr;
     int64_t mipsFrame = -1;  // frame index the chains were built from
     bool autoMips = false;   // rebuild them at the end of every frame, as the reference does
-    unsigned long long* mipsDone = nullptr;  // device counter the chain kernels bump when they stop reading
-    unsigned long long mipsSignals = 0;      // its value once every chain launched so far has finished
+    // readers of a frame's outputs that run beside the next frame (mip chains, host pack)
+    unsigned long long* auxDone = nullptr;  // device counter they bump when they stop reading
+    unsigned long long auxSignals = 0;      // its value once every reader launched so far has finished
     // surface-sample scratch: n x (2 in + 7 out) floats
     float* sBuf = nullptr;
     int sCap = 0;
@@ -305,7 +334,7 @@ struct OceanHandle {
 
     int Awake(const float* noiseHost, uint64_t seed);
     int CalculateInitialSpectrumTextures();
-    int CalculateWavesTexturesAtTime(float time, int which = 0);
+    int CalculateWavesTexturesAtTime(float time, int which = 0, float* heightOut = nullptr);
     int Update(float time);
     void PollReadbacks(bool wait);
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
@@ -362,6 +391,8 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
         OCEAN_CUDA(cudaMallocHost(&rbHost[i], layerBytes4()));
         OCEAN_CUDA(cudaEventCreateWithFlags(&rbDone[i], cudaEventDisableTiming));
     }
+    OCEAN_CUDA(cudaMalloc(&auxDone, sizeof(unsigned long long)));
+    OCEAN_CUDA(cudaMemsetAsync(auxDone, 0, sizeof(unsigned long long), stream));
     OCEAN_CUDA(cudaEventCreateWithFlags(&rbSnap, cudaEventDisableTiming));
     OCEAN_CUDA(cudaStreamSynchronize(stream));  // host staging (tw, seed) may go out of scope
     return OCEAN_OK;
@@ -381,7 +412,7 @@ int OceanHandle::CalculateInitialSpectrumTextures() {
     return OCEAN_OK;
 }
 
-int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
+int OceanHandle::CalculateWavesTexturesAtTime(float time, int which, float* heightOut) {
     if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_step before ocean_init_spectrum");
     FrameArgs a{};
     a.N = N; a.layers = C; a.C = C;
@@ -396,9 +427,10 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which) {
     if (doRows && rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "row pass issued twice without a column pass");
     if (doCols && !doRows && !rowsPending) return fail(OCEAN_ERR_INVALID_ARGUMENT, "column pass without a preceding row pass");
     workspace_stamp(ws, N, doRows, doCols, &a);
-    a.mipsDone = mipsDone;  // nullptr until a chain has been built on this ocean
-    a.mipsTarget = mipsSignals;
-    if (which == 0 && !mipsDone && frame_fused_available(N, &colsMaps)) {
+    a.auxDone = auxSignals ? auxDone : nullptr;  // only once a reader has been launched on this ocean
+    a.auxTarget = auxSignals;
+    a.heightOut = heightOut;
+    if (which == 0 && !auxSignals && !heightOut && frame_fused_available(N, &colsMaps)) {
         OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
         foamZero = false;
         ++frame;
@@ -423,13 +455,9 @@ int OceanHandle::GenerateMips() {
     const size_t bytes = (size_t)C * mip_texels_per_layer(N) * sizeof(float4);
     if (!derivMips) OCEAN_CUDA(cudaMalloc(&derivMips, bytes));
     if (!turbMips) OCEAN_CUDA(cudaMalloc(&turbMips, bytes));
-    if (!mipsDone) {
-        OCEAN_CUDA(cudaMalloc(&mipsDone, sizeof(unsigned long long)));
-        OCEAN_CUDA(cudaMemsetAsync(mipsDone, 0, sizeof(unsigned long long), stream));
-    }
     unsigned long long signals = 0;
-    OCEAN_CUDA(launch_mip_chains(deriv, derivMips, turb, turbMips, N, C, mipsDone, &signals, stream));
-    mipsSignals += signals;
+    OCEAN_CUDA(launch_mip_chains(deriv, derivMips, turb, turbMips, N, C, auxDone, &signals, stream));
+    auxSignals += signals;
     mipsFrame = frame;
     return OCEAN_OK;
 }
@@ -467,46 +495,80 @@ int OceanHandle::SampleSurface(const float* worldXZ, int n, float lod, float* di
     return OCEAN_OK;
 }
 
+// Has slot i's request completed?  wait: block until it has.
+bool OceanHandle::SlotDone(int i, bool wait) {
+    cudaError_t e = wait ? cudaEventSynchronize(rbDone[i]) : cudaEventQuery(rbDone[i]);
+    if (e == cudaErrorNotReady) cudaGetLastError();
+    return e == cudaSuccess;
+}
+
 void OceanHandle::PollReadbacks(bool wait) {
     for (int i = 0; i < RB; ++i) {
         if (!rbPending[i]) continue;
-        cudaError_t e = wait ? cudaEventSynchronize(rbDone[i]) : cudaEventQuery(rbDone[i]);
-        if (e == cudaSuccess) {
+        if (SlotDone(i, wait)) {
             rbPending[i] = false;
             if (rbLatest < 0 || rbFrame[i] > rbFrame[rbLatest]) rbLatest = i;
-        } else if (e == cudaErrorNotReady) {
-            cudaGetLastError();
         }
     }
 }
 
+#ifdef OCEAN_HOST_PROF
+#include <chrono>
+static double g_prof[8]; static long g_profN;
+struct ProfT { int k; std::chrono::steady_clock::time_point t0; ProfT(int k) : k(k), t0(std::chrono::steady_clock::now()) {}
+    ~ProfT() { g_prof[k] += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count(); } };
+#define PROF(k) ProfT prof_##k(k)
+extern "C" void ocean_debug_host_prof() { for (int i = 0; i < 8; ++i) printf("prof[%d] = %.2f us/update\n", i, g_prof[i] / (g_profN ? g_profN : 1)); }
+#else
+#define PROF(k)
+#endif
 int OceanHandle::Update(float time) {
-    int rc = CalculateWavesTexturesAtTime(time);
-    if (rc != OCEAN_OK) return rc;
+#ifdef OCEAN_HOST_PROF
+    ++g_profN;
+#endif
+    PROF(0);
+    if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_update before ocean_init_spectrum");
     // pick a slot that is neither in flight nor the visible buoyancyData
     int s = -1;
-    for (;;) {
-        PollReadbacks(false);
-        for (int i = 0; i < RB && s < 0; ++i)
-            if (!rbPending[i] && i != rbLatest) s = i;
-        if (s >= 0) break;
-        int oldest = -1;
-        for (int i = 0; i < RB; ++i)
-            if (rbPending[i] && (oldest < 0 || rbFrame[i] < rbFrame[oldest])) oldest = i;
-        OCEAN_CUDA(cudaEventSynchronize(rbDone[oldest]));
+    {
+        PROF(2);
+        for (;;) {
+            PollReadbacks(false);
+            for (int i = 0; i < RB && s < 0; ++i)
+                if (!rbPending[i] && i != rbLatest) s = i;
+            if (s >= 0) break;
+            int oldest = -1;
+            for (int i = 0; i < RB; ++i)
+                if (rbPending[i] && (oldest < 0 || rbFrame[i] < rbFrame[oldest])) oldest = i;
+            if (!SlotDone(oldest, true)) return fail(OCEAN_ERR_CUDA, "readback of frame %lld did not complete", (long long)rbFrame[oldest]);
+        }
     }
-    // snapshot layer 0 on the compute stream, ship it to the host on the copy stream
-    size_t bytes = layerBytes4();
-    if (rbMode == OCEAN_READBACK_HEIGHT) {
-        bytes = texels() * sizeof(float);
-        OCEAN_CUDA(launch_pack_height(disp, (float*)rbStage[s], (int)texels(), stream));
+    if (rbMode == OCEAN_READBACK_HEIGHT && stream_wait_value_available()) {
+        // Only the channel GetWaterHeight reads (WB:206-208): the column pass writes it into the slot's staging
+        // plane; the copy stream starts as soon as the columns of layer 0 are done.
+        int rc;
+        { PROF(1); rc = CalculateWavesTexturesAtTime(time, 0, (float*)rbStage[s]); }
+        if (rc != OCEAN_OK) return rc;
+        const unsigned long long* colsDone0 = ws->counters + ws->layers;  // layer 0 of this ocean
+        { PROF(4); OCEAN_CUDA(stream_wait_value_geq(copyStream, colsDone0, (unsigned long long)N * ws->colPasses)); }
+        { PROF(5); OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], texels() * sizeof(float), cudaMemcpyDeviceToHost, copyStream)); }
+        { PROF(6); OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream)); }
     } else {
-        OCEAN_CUDA(cudaMemcpyAsync(rbStage[s], disp, bytes, cudaMemcpyDeviceToDevice, stream));
+        int rc = CalculateWavesTexturesAtTime(time);
+        if (rc != OCEAN_OK) return rc;
+        // snapshot layer 0 on the compute stream, ship it to the host on the copy stream (WB:288: the whole layer)
+        size_t bytes = layerBytes4();
+        if (rbMode == OCEAN_READBACK_HEIGHT) {
+            bytes = texels() * sizeof(float);
+            OCEAN_CUDA(launch_pack_height(disp, (float*)rbStage[s], (int)texels(), stream));
+        } else {
+            OCEAN_CUDA(cudaMemcpyAsync(rbStage[s], disp, bytes, cudaMemcpyDeviceToDevice, stream));
+        }
+        OCEAN_CUDA(cudaEventRecord(rbSnap, stream));
+        OCEAN_CUDA(cudaStreamWaitEvent(copyStream, rbSnap, 0));
+        OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], bytes, cudaMemcpyDeviceToHost, copyStream));
+        OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
     }
-    OCEAN_CUDA(cudaEventRecord(rbSnap, stream));
-    OCEAN_CUDA(cudaStreamWaitEvent(copyStream, rbSnap, 0));
-    OCEAN_CUDA(cudaMemcpyAsync(rbHost[s], rbStage[s], bytes, cudaMemcpyDeviceToHost, copyStream));
-    OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
     rbSlotMode[s] = rbMode;
     rbFrame[s] = frame - 1;
     rbPending[s] = true;
@@ -570,7 +632,7 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, mipsDone};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, auxDone};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {

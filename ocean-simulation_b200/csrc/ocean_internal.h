@@ -79,11 +79,14 @@ struct FrameArgs {
     // next frame may overwrite its rows of the workspace once colsDone[layer] >= colsTarget.
     unsigned long long* colsDone;      // device, one counter per layer
     unsigned long long colsTarget;     // N * (column passes issued before this frame)
-    // Mip chains (WB:191-192) read deriv / turb after a frame without holding the next frame back: the
-    // column pass waits for mipsDone >= mipsTarget before it overwrites those two arrays (nullptr: no chain
-    // was ever built on this ocean).
-    const unsigned long long* mipsDone;
-    unsigned long long mipsTarget;
+    // Readers of a frame's outputs that run beside the next frame (mip chains WB:191-192, the host pack of
+    // the readback WB:288) do not hold its row pass back: the column pass waits for auxDone >= auxTarget
+    // before its first store instead (nullptr: no such reader was ever launched on this ocean).
+    const unsigned long long* auxDone;
+    unsigned long long auxTarget;
+    // Readback plane (WB:288, HEIGHT mode): when not nullptr the column pass also writes the .g channel of
+    // displacement layer 0 here, N*N floats; it is complete once colsDone[0] reaches this frame's count.
+    float* heightOut;
     // Ensembles: when not nullptr the column pass adds, per state (= layer / C), the 64-bit sums of the fp32
     // bit patterns of the texels it produces to checksums[state * 3 + {0: disp, 1: deriv, 2: turb}].
     unsigned long long* checksums;
