@@ -459,6 +459,10 @@ int OceanHandle::GenerateMips() {
     OCEAN_CUDA(launch_mip_chains(deriv, derivMips, turb, turbMips, N, C, auxDone, &signals, stream));
     auxSignals += signals;
     mipsFrame = frame;
+    // (Building the chains on a side stream gated by the column counters was measured and dropped: with the
+    // next column pass spinning for them, back-to-back frames starved the chain kernels of SM resources and
+    // deadlocked; ordering that pass after them with an event instead cost 43.0 us per frame + chains
+    // against 38.7 us for this in-stream programmatic chain.)
     return OCEAN_OK;
 }
 
@@ -1060,6 +1064,7 @@ int ocean_set_stream(OceanHandle* h, void* s) {
     if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
     DeviceScope scope(h->device);
     OCEAN_CUDA(cudaStreamSynchronize(h->stream));
+    OCEAN_CUDA(cudaStreamSynchronize(h->copyStream));  // a pending readback waits on the old workspace's counters
     h->stream = s ? (cudaStream_t)s : h->ownStream;
     return h->AttachWorkspace(s ? (cudaStream_t)s : nullptr);
 }

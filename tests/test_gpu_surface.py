@@ -55,6 +55,26 @@ def test_auto_mips_follow_every_frame(pkg, po, so):
     body.OnDisable()
 
 
+def test_auto_mips_with_back_to_back_frames_and_readbacks(pkg, po, so):
+    """200 frames enqueued without a host sync, chains rebuilt beside every next frame and a height readback per
+    frame: nothing deadlocks, and the final chains belong to the final arrays."""
+    L = pkg._lib
+    cfg, body, _ = stepped_body(pkg, po, N=None, frames=1)  # 4 x 512^2: the headline kernels
+    body.GenerateMips(auto=True)
+    body.SetReadbackMode(L.READBACK_HEIGHT)
+    for f in range(200):
+        body.Update(0.7 + f / 60.0)
+    body.Sync()
+    frame, heights = body.WaitReadback()
+    assert frame == body.frame - 1
+    assert np.array_equal(heights, body.displacementsTextures[0][..., 1])
+    for which, arr in ((L.DERIVATIVES, body.derivativesTextures), (L.TURBULENCE, body.turbulenceTextures)):
+        want = so.mip_chain(arr[2])
+        for level in (1, 4, 9):
+            assert np.array_equal(body.Mip(which, level, 2), want[level])
+    body.OnDisable()
+
+
 @pytest.mark.parametrize("lod", [0.0, 1.0, 2.6, 40.0])
 def test_surface_sample_bit_exact_on_the_library_arrays(pkg, po, so, lod):
     cfg, body, _ = stepped_body(pkg, po)
