@@ -7,9 +7,6 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "r2m7": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
-    "r2m6": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=6"],
-    "r1m12": ["-DOCEAN_ROWS512_MINB=12"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()

@@ -11,7 +11,7 @@ def build():
     bm = oceanpkg.build_module(); bm.build()
     obj = os.path.join(HERE, "frame_trace.o")
     subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + ["-DOCEAN_TRACE"] + EXTRA + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj])
-    others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o")]
+    others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o", "ocean_surface.o")]
     subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", LIB, obj] + others)
     os.remove(obj)
 
@@ -31,6 +31,9 @@ def main():
         b.SetStream(st.cuda_stream); bodies.append(b)
     for f in range(24): bodies[f % 4].CalculateWavesTexturesAtTime(f / 60.0)
     torch.cuda.synchronize()
+    if "--standalone" in sys.argv:  # one row pass and one column pass, each alone on the GPU
+        bodies[0].StepPartial(0.5, 1); torch.cuda.synchronize()
+        bodies[0].StepPartial(0.5, 2); torch.cuda.synchronize()
     CT, SL = 8192, 10
     times = np.zeros((2, CT, SL, 2), np.uint64); smid = np.zeros((2, CT), np.uint32)
     lib.ocean_debug_trace_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
@@ -66,6 +69,12 @@ def main():
         print("  layer %d: rows start %.1f..%.1f end %.1f..%.1f | cols A arrived %.1f..%.1f  tile end %.1f..%.1f" % (L, rs.min(), rs.max(), re.min(), re.max(), ca.min(), ca.max(), ce.min(), ce.max()))
     # CTAs per SM
     sm = smid[0, :nr]; print("rows CTAs per SM: min %d max %d" % (np.bincount(sm).min(), np.bincount(sm).max()))
+    # CTA dispatch: start times of the row CTAs of a few SMs, in order
+    t0 = g[0, :nr, 0]; t0 = (t0 - t0.min()) / 1e3
+    for s_ in (0, 1, 73, 147):
+        v = np.sort(t0[sm == s_]); print("  SM %3d row CTA starts (us):" % s_, " ".join("%.2f" % x for x in v))
+    te = g[0, :nr, 7]; te = (te - g[0, :nr, 0].min()) / 1e3
+    print("  rows kernel span: first start 0.00, last start %.2f, first end %.2f, last end %.2f" % (t0.max(), te.min(), te.max()))
 
 if __name__ == "__main__":
     main()
