@@ -13,6 +13,7 @@
 // Bandwidth-bound fp32 FFT: tensor cores are not used (no dense contraction here).
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <utility>
 
@@ -1031,15 +1032,21 @@ template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsT
     return launch_pdl(early, a, ocean_frame_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a);
 }
 static bool tma_size(int N) { return N == 256 || N == 512 || N == 1024; }
-// Opt-in (OCEAN_FUSED=1 or -DOCEAN_USE_FUSED): measured 29.3 us/frame against 26.9 us for the
-// two-kernel path at 4 x 512^2 -- its items still wait for their just-in-time loads.
+// The whole frame as one persistent kernel.  Default at N = 256, where the frame is a latency chain and one
+// launch beats two (config 1: 9.3 vs 10.5 us, config 2: 10.0 vs 13.0 us).  At N = 512 the two-kernel path
+// wins (26.5 vs 29.4 us at 4 x 512^2: the fused kernel's items still wait for their just-in-time loads, see
+// DESIGN.md).  OCEAN_FUSED=0 / 1 (or -DOCEAN_USE_FUSED) forces it off / on for both sizes.
 bool frame_fused_available(int N, const ColsTmaMaps* maps) {
+    if (!(N == 256 || N == 512) || !maps || !maps->valid) return false;
 #ifdef OCEAN_USE_FUSED
-    const bool on = true;
+    return true;
 #else
-    static const bool on = getenv("OCEAN_FUSED") != nullptr;
+    static const int mode = [] {
+        const char* e = getenv("OCEAN_FUSED");
+        return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1);
+    }();
+    return mode < 0 ? N == 256 : mode == 1;
 #endif
-    return on && (N == 256 || N == 512) && maps && maps->valid;
 }
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early) {
     if (a.N == 512) return frame_launch<512>(a, *maps, s, early);
@@ -1093,7 +1100,7 @@ template <int N> static cudaError_t configure() {
     return cudaSuccess;
 }
 template <int N> static const char* describe() {
-    static char buf[512];
+    static char buf[768];
     if (N == 1024 || N == 512 || N == 256) {
         constexpr int M = (N == 1024 || N == 512 || N == 256) ? N : 512;
         snprintf(buf, sizeof buf,
@@ -1101,6 +1108,10 @@ template <int N> static const char* describe() {
                  "cols_tma<N=%d>: persistent warp-specialised, %d columns/tile, %d threads, %d B smem (TMA in, TMA out)",
                  N, RowCfg<N>::R, RowCfg<N>::THREADS, RowCfg<N>::SMEM_BYTES, N, ColTmaCfg<M>::W, ColTmaCfg<M>::THREADS,
                  ColTmaCfg<M>::SMEM_BYTES);
+        if (N == 256) {
+            const size_t n = strlen(buf);
+            snprintf(buf + n, sizeof buf - n, "; whole frames run as one fused persistent kernel (ocean_frame_kernel) unless OCEAN_FUSED=0");
+        }
         return buf;
     }
     snprintf(buf, sizeof buf,
