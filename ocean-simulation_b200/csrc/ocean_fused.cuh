@@ -286,8 +286,13 @@ ocean_frame_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs a) 
             for (int j = 0; j < 8; ++j) r[j] = c2_load(&bufA[(tid + T * j) * W + xw]);
             ColFFT::run(r, bufA, tid, xw, twS, 0);
             ColFFT::barrier();  // every thread has finished reading the last exchange
+            const bool heights = a.heightOut != nullptr && it.layer == 0;  // the readback plane of WB:288 (.g only)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) bufA[(tid + T * j) * W + xw] = ep.displacement(r[j], dxz[j]);
+            for (int j = 0; j < 8; ++j) {
+                const float4 v = ep.displacement(r[j], dxz[j]);
+                bufA[(tid + T * j) * W + xw] = v;
+                if (heights) a.heightOut[(size_t)(tid + T * j) * N + x] = v.y;
+            }
             fence_proxy_async();
             mbar_arrive(&bars[2]);
             TRACE(0, pos, 3);

@@ -430,7 +430,7 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which, float* heig
     a.auxDone = auxSignals ? auxDone : nullptr;  // only once a reader has been launched on this ocean
     a.auxTarget = auxSignals;
     a.heightOut = heightOut;
-    if (which == 0 && !auxSignals && !heightOut && frame_fused_available(N, &colsMaps)) {
+    if (which == 0 && !auxSignals && frame_fused_available(N, &colsMaps)) {
         OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
         foamZero = false;
         ++frame;

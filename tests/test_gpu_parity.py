@@ -326,20 +326,22 @@ def test_update_readback_and_get_water_height(pkg, po):
     body.OnDisable()
 
 
-def test_height_only_readback_answers_like_the_rgba_readback(pkg, po):
-    """OCEAN_READBACK_HEIGHT ships only `.g` of layer 0 (what WB:206-208 reads); GetWaterHeight is unchanged."""
-    cfg = pkg.scene.config(1)
-    body, _ = make_body(pkg, po, cfg, N=128)
+@pytest.mark.parametrize("N", [128, 256, 512, 1024])  # plain-load columns, fused frame kernel, TMA columns (2 shapes)
+def test_height_only_readback_answers_like_the_rgba_readback(pkg, po, N):
+    """OCEAN_READBACK_HEIGHT ships only `.g` of layer 0 (what WB:206-208 reads); GetWaterHeight is unchanged.
+    The height plane is written by whichever column kernel the size selects."""
+    cfg = pkg.scene.config(2)
+    body, _ = make_body(pkg, po, cfg, N=N)
     L = pkg._lib
     pts = [(3.0, 0.0, -7.0), (-63.5, 0.0, 63.9), (0.0, 0.0, 0.0), (500.0, 0.0, -500.0)]
     body.Update(0.5)
     frame, rgba = body.WaitReadback()
-    assert frame == 0 and rgba.shape == (128, 128, 4)
+    assert frame == 0 and rgba.shape == (N, N, 4)
     want = [body.GetWaterHeight(p) for p in pts]
     body.SetReadbackMode(L.READBACK_HEIGHT)
     body.Update(0.5)  # same time: same displacement (only the foam recursion advances)
     frame, h = body.WaitReadback()
-    assert frame == 1 and h.shape == (128, 128)
+    assert frame == 1 and h.shape == (N, N)
     assert np.array_equal(h, rgba[..., 1]) and np.array_equal(h, body.displacementsTextures[0][..., 1])
     assert [body.GetWaterHeight(p) for p in pts] == want
     body.OnDisable()
