@@ -23,9 +23,20 @@
 
 namespace ocean {
 
+// L2 residency of the row->column workspace.  Measured at 4 x 512^2 (4 rotating oceans / one ocean), us per
+// frame: no hints 26.6 / 26.0; 6 = output stores evict_first + workspace stores evict_last 25.7-26.0 / 25.1-25.4;
+// also marking the workspace or turbulence loads (7, 14, 15) is no better; evict_first on the workspace loads 27.4.
+#ifndef OCEAN_L2_HINTS
+#define OCEAN_L2_HINTS 6  // bit 0: workspace TMA loads evict_last, bit 1: output TMA stores evict_first, bit 2: workspace stores evict_last, bit 3: turbulence TMA load evict_first
+#endif
+
 // Streaming (read-once / write-once) accesses keep the intermediate resident in L2.
 __device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
+// 16-byte global store of a C2 with an L2 eviction policy (ocean_tma.cuh constants)
+__device__ __forceinline__ void c2_store_hint(float4* p, const C2& v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.v2.u64 [%0], {%1, %2}, %3;" ::"l"(p), "l"(v.re), "l"(v.im), "l"(policy) : "memory");
+}
 // read-once 8-byte load that does not allocate in L1 (the twiddle table should own what L1 is left)
 __device__ __forceinline__ float2 ld_once(const float2* p) {
     float2 v;
@@ -217,6 +228,15 @@ __device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
 #endif
 
 // ---------------------------------------------------------------------------------------------
+// workspace stores of the row pass
+__device__ __forceinline__ void ws_store(float4* p, const C2& v) {
+#if OCEAN_L2_HINTS & 4
+    c2_store_hint(p, v, L2_EVICT_LAST);
+#else
+    c2_store(p, v);
+#endif
+}
+
 template <int N>
 __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_rows_kernel(const FrameArgs a) {
     using Cfg = RowCfg<N>;
@@ -313,9 +333,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         float4* __restrict__ outA = a.rowsA + line * N;
         float4* __restrict__ outB = a.rowsB + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&outA[tid + T * j], pa[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&outA[tid + T * j], pa[j]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&outB[tid + T * j], pb[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&outB[tid + T * j], pb[j]);
     }
     TRACE(0, blockIdx.x, 5);
     TRACE(0, blockIdx.x, 6);
@@ -331,7 +351,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pa[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pa[j]);
     }
     TRACE(0, blockIdx.x, 5);
     FFT::run(pb, smem, tid, row, a.twiddle, FFT::EXCHANGES);
@@ -339,7 +359,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (active) {
         float4* __restrict__ out = a.rowsB + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pb[j]);
     }
 #endif
     // publish: this CTA's rows of both planes are in memory (visible to the TMA loads of the column pass)
@@ -496,7 +516,7 @@ __global__ void __launch_bounds__(RowPairCfg<N>::THREADS, RowPairCfg<N>::MINB) o
     {
         float4* __restrict__ out = a.rowsA + rowBase;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], v[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], v[j]);
     }
     TRACE(0, blockIdx.x, 5);
 #pragma unroll
@@ -506,7 +526,7 @@ __global__ void __launch_bounds__(RowPairCfg<N>::THREADS, RowPairCfg<N>::MINB) o
     {
         float4* __restrict__ out = a.rowsB + rowBase;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], v[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], v[j]);
     }
     // publish: both rows of both planes are in memory (visible to the TMA loads of the column pass)
     __syncthreads();
@@ -685,8 +705,15 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         auto load = [&](const CUtensorMap* map, float4* buf, uint64_t* bar, int tile) {
             int c0, c1;
             coords(tile, c0, c1);
+            const bool isTurb = map == &maps.turb;
 #pragma unroll
-            for (int b = 0; b < Cfg::NBOX; ++b) tma_load_2d(buf + b * Cfg::BOX_ROWS * W, map, bar, c0, c1 + b * Cfg::BOX_ROWS);
+            for (int b = 0; b < Cfg::NBOX; ++b) {
+                float4* dst = buf + b * Cfg::BOX_ROWS * W;
+                const int r0 = c1 + b * Cfg::BOX_ROWS;
+                if ((OCEAN_L2_HINTS & 1) && !isTurb) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_LAST);       // workspace: stays put
+                else if ((OCEAN_L2_HINTS & 8) && isTurb) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_FIRST);  // read once
+                else tma_load_2d(dst, map, bar, c0, r0);
+            }
         };
         // pair B travels with the tile's incoming turbulence texels (RF:28), which land in bufT
         const bool needFoam = a.zeroFoam == 0;
@@ -699,7 +726,13 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             int c0, c1;
             coords(tile, c0, c1);
 #pragma unroll
-            for (int b = 0; b < Cfg::NBOX; ++b) tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, c0, c1 + b * Cfg::BOX_ROWS);
+            for (int b = 0; b < Cfg::NBOX; ++b) {
+#if OCEAN_L2_HINTS & 2
+                tma_store_2d_hint(map, buf + b * Cfg::BOX_ROWS * W, c0, c1 + b * Cfg::BOX_ROWS, L2_EVICT_FIRST);  // written once
+#else
+                tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, c0, c1 + b * Cfg::BOX_ROWS);
+#endif
+            }
         };
         int readyLayer = -1;  // layers are polled once: counters only grow
         auto await_rows = [&](int tile) {

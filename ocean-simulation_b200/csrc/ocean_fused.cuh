@@ -83,7 +83,8 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
     auto tile_store = [&](const CUtensorMap* map, const float4* buf, const FrameItem& it) {
 #pragma unroll
         for (int b = 0; b < Cfg::NBOX; ++b)
-            tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, it.idx * W * 4, it.layer * N + b * Cfg::BOX_ROWS);
+            if (OCEAN_L2_HINTS & 2) tma_store_2d_hint(map, buf + b * Cfg::BOX_ROWS * W, it.idx * W * 4, it.layer * N + b * Cfg::BOX_ROWS, L2_EVICT_FIRST);
+            else tma_store_2d(map, buf + b * Cfg::BOX_ROWS * W, it.idx * W * 4, it.layer * N + b * Cfg::BOX_ROWS);
     };
     auto row_offset = [&](const FrameItem& it) { return ((size_t)it.layer * N + (size_t)it.idx * W) * N; };
     // a column item needs its layer's rows of THIS frame; a row item's inputs are immutable
@@ -135,7 +136,8 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
         if (cur.role == 0) {
             // write-after-read on the workspace: the previous frame's columns of this layer are done
             spin_until_ge(a.colsDone + cur.layer, a.colsTarget);
-            bulk_store_1d(a.rowsA + row_offset(cur), bufA, TILE_BYTES);
+            if (OCEAN_L2_HINTS & 4) bulk_store_1d_hint(a.rowsA + row_offset(cur), bufA, TILE_BYTES, L2_EVICT_LAST);
+            else bulk_store_1d(a.rowsA + row_offset(cur), bufA, TILE_BYTES);
         } else {
             tile_store(&maps.disp, bufA, cur);
         }
@@ -145,7 +147,8 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
 
         mbar_wait(&bars[3], parity);  // part B staged in bufB (and bufT)
         if (cur.role == 0) {
-            bulk_store_1d(a.rowsB + row_offset(cur), bufB, TILE_BYTES);
+            if (OCEAN_L2_HINTS & 4) bulk_store_1d_hint(a.rowsB + row_offset(cur), bufB, TILE_BYTES, L2_EVICT_LAST);
+            else bulk_store_1d(a.rowsB + row_offset(cur), bufB, TILE_BYTES);
         } else {
             tile_store(&maps.deriv, bufB, cur);
             tile_store(&maps.turb, bufT, cur);

@@ -13,6 +13,11 @@ namespace ocean {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// L2 eviction policies for the .L2::cache_hint forms below (the pre-encoded fractional policies CUTLASS uses)
+constexpr uint64_t L2_EVICT_NORMAL = 0x1000000000000000ull;
+constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull;
+constexpr uint64_t L2_EVICT_LAST = 0x14F0000000000000ull;
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t arrivals) {
@@ -81,6 +86,11 @@ __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smemSrc, u
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smemSrc)), "r"(bytes)
                  : "memory");
 }
+__device__ __forceinline__ void bulk_store_1d_hint(void* gdst, const void* smemSrc, uint32_t bytes, uint64_t policy) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(smem_u32(smemSrc)),
+                 "r"(bytes), "l"(policy)
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // every committed bulk group has finished READING its shared-memory source (the buffer may be reused)
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
@@ -98,6 +108,22 @@ __device__ __forceinline__ void tma_load_2d(void* smemDst, const CUtensorMap* ma
             smem_u32(smemDst)),
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+
+// The same tensor copies with an L2 eviction policy (the pre-encoded fractional policies CUTLASS uses:
+// every line of the access gets the priority).  evict_first marks read-once inputs and write-once outputs so
+// that they do not push the row->column workspace out of L2; evict_last keeps a line until normal ones are gone.
+__device__ __forceinline__ void tma_load_2d_hint(void* smemDst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(
+            smem_u32(smemDst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_2d_hint(const CUtensorMap* map, const void* smemSrc, int c0, int c1, uint64_t policy) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(map),
+                 "r"(smem_u32(smemSrc)), "r"(c0), "r"(c1), "l"(policy)
+                 : "memory");
 }
 
 }  // namespace ocean

@@ -7,6 +7,10 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
+    "h06": ["-DOCEAN_COLS_L2_HINTS=6"],
+    "h07": ["-DOCEAN_COLS_L2_HINTS=7"],
+    "h14": ["-DOCEAN_COLS_L2_HINTS=14"],
+    "h15": ["-DOCEAN_COLS_L2_HINTS=15"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
