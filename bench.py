@@ -239,9 +239,10 @@ def run_cuda(args):
                        "kernels": describe},
             "e2e": {"value": world * K * C / t_e2e, "unit": UNIT, "h2d_bytes_per_step": 4,
                     "d2h_bytes_per_step": N * N * 4, "ms_per_step": 1e3 * t_e2e / K,
-                    "what": "ocean_update through the C ABI, host wall clock: frame + pack + async readback to pinned host "
-                            "memory of the height channel of displacement layer 0 (what GetWaterHeight WB:195-209 reads; "
-                            "WaterBody.Update WB:284-297); the only per-step host input is the time scalar",
+                    "what": "ocean_update through the C ABI, host wall clock: frame + async readback to pinned host memory of the "
+                            "height channel of displacement layer 0 (what GetWaterHeight WB:195-209 reads; WaterBody.Update "
+                            "WB:284-297; the column pass writes the plane, the copy stream is released by the layer-0 column "
+                            "counter); the only per-step host input is the time scalar",
                     "rgba_readback": {"value": world * K * C / t_e2e_rgba, "ms_per_step": 1e3 * t_e2e_rgba / K,
                                       "d2h_bytes_per_step": N * N * 16,
                                       "what": "same with the reference's whole-layer RGBA32F request (WB:288), PCIe-bound"}},
