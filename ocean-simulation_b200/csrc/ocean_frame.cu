@@ -103,6 +103,12 @@ __device__ __forceinline__ void trace_mark(int kernel, int cta, int slot) {
 #ifndef OCEAN_ROWS512_R
 #define OCEAN_ROWS512_R 1
 #endif
+#ifndef OCEAN_ROWS1024_MINB
+#define OCEAN_ROWS1024_MINB 7
+#endif
+#ifndef OCEAN_ROWS2048_MINB
+#define OCEAN_ROWS2048_MINB 3
+#endif
 #ifndef OCEAN_ROWS512_MINB
 #define OCEAN_ROWS512_MINB 14
 #endif
@@ -169,7 +175,8 @@ template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
     static constexpr int THREADS = R * T;
-    static constexpr int MINB = (N == 512) ? OCEAN_ROWS512_MINB : 1;
+    // 72 registers per thread (as many warps per SM as at N = 512) for the one-row-per-CTA sizes
+    static constexpr int MINB = (N == 512) ? OCEAN_ROWS512_MINB : (N == 1024 ? OCEAN_ROWS1024_MINB : (N == 2048 ? OCEAN_ROWS2048_MINB : 1));
     // the staged h0 row doubles as the (single) exchange buffer; every exchange is swizzled
     using FFT = LineFFT<N, R, false, false, false>;
 #if OCEAN_ROWS_WAVE_REGS
