@@ -30,12 +30,12 @@ __device__ __forceinline__ u64 pk2(float lo, float hi) {
     return r;
 }
 __device__ __forceinline__ float lo2(u64 v) {
-    float a, b;
+    [[maybe_unused]] float a, b;
     asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
     return a;
 }
 __device__ __forceinline__ float hi2(u64 v) {
-    float a, b;
+    [[maybe_unused]] float a, b;
     asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
     return b;
 }

@@ -251,7 +251,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     constexpr int T = Cfg::T, R = Cfg::R;
     extern __shared__ float4 smem[];
     float4* hs = smem;                             // [R][N] staged h0, then the exchange buffer
+#if !OCEAN_ROWS_WAVE_REGS
     float2* ws = (float2*)(smem + R * N);          // [R][N] staged (1/|k|, omega)
+#endif
     const int tid = threadIdx.x & (T - 1);
     const int row = threadIdx.x / T;
     const size_t totalRows = (size_t)a.layers * N;
