@@ -216,7 +216,10 @@ void ocean_ensemble_destroy(OceanEnsemble* e);
  * Asynchronous work is drained before returning. */
 int ocean_ensemble_run(OceanEnsemble* e, const OceanParams* states, const uint64_t* seeds, int nStates,
                        float time, uint64_t* checksums);
-/* Device pointers of the pooled output arrays of the last wave ([batch*C][N][N][4]). */
+/* Device pointers of the pooled arrays of the last wave ([batch*C][N][N][4]): the three outputs and
+ * OCEAN_INITIAL_SPECTRUM.  Waves alternate between two sets of pooled buffers (two lanes, so that the
+ * ALU-bound spectrum kernels of one wave overlap the memory-bound frame of the other); the pointers are
+ * those of the lane that ran the last wave.  OCEAN_WAVES_DATA is not kept by ensembles. */
 int ocean_ensemble_get_output(OceanEnsemble* e, int which, void** devPtr, size_t* bytes);
 int ocean_ensemble_copy_output(OceanEnsemble* e, int which, int slot, float* host /* C*N*N*4 */);
 

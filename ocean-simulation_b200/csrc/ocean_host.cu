@@ -650,25 +650,37 @@ void OceanHandle::OnDisable() {
 
 // ---------------------------------------------------------------------------------------------
 // Ensemble runner: waves of `batch` independent oceans through pooled buffers.
-struct OceanEnsemble {
-    int device = 0, N = 0, C = 0, batch = 0;
-    OceanCascade cascades[OCEAN_MAX_CASCADES]{};
+//
+// Two lanes.  A wave is noise -> initial spectrum (ALU-bound: ~17 transcendentals per texel-cascade)
+// -> row pass -> column pass (memory-bound).  Each lane owns a stream and a full set of pooled buffers;
+// consecutive waves alternate between the lanes, so the ALU-bound kernels of one wave share the SMs with
+// the memory-bound kernels of the other instead of running after them (OCEAN_ENSEMBLE_LANES=1: one lane).
+struct EnsembleLane {
     cudaStream_t stream = nullptr;
     float2* noise = nullptr;
-    float4 *h0 = nullptr, *wave = nullptr, *rowsA = nullptr, *rowsB = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
-    Workspace* ws = nullptr;
+    float4 *h0 = nullptr, *disp = nullptr, *deriv = nullptr, *turb = nullptr;
     float2* waveHot = nullptr;
     float2* h0c = nullptr;
+    Workspace* ws = nullptr;
     ColsTmaMaps colsMaps;
+    // parameter / result staging of the wave in flight on this lane
+    StateConsts* stateDev = nullptr;
+    uint64_t* seedDev = nullptr;
+    unsigned long long* sumDev = nullptr;
+    StateConsts* stateHost = nullptr;
+    uint64_t* seedHost = nullptr;
+    unsigned long long* sumHost = nullptr;
+    cudaEvent_t done = nullptr;
+};
+
+struct OceanEnsemble {
+    static constexpr int MAX_LANES = 2;
+    int device = 0, N = 0, C = 0, batch = 0;
+    int lanes = MAX_LANES;
+    OceanCascade cascades[OCEAN_MAX_CASCADES]{};
+    EnsembleLane lane[MAX_LANES];
     float2* twiddle = nullptr;
-    // double-buffered parameter / result staging so consecutive waves overlap
-    StateConsts* stateDev[2] = {nullptr, nullptr};
-    uint64_t* seedDev[2] = {nullptr, nullptr};
-    unsigned long long* sumDev[2] = {nullptr, nullptr};
-    StateConsts* stateHost[2] = {nullptr, nullptr};
-    uint64_t* seedHost[2] = {nullptr, nullptr};
-    unsigned long long* sumHost[2] = {nullptr, nullptr};
-    cudaEvent_t done[2] = {nullptr, nullptr};
+    int lastLane = 0;   // the lane that ran the last wave (ocean_ensemble_get_output)
     int lastCount = 0;
 
     size_t stateFloat4() const { return (size_t)C * N * N; }
@@ -679,31 +691,30 @@ struct OceanEnsemble {
 
 int OceanEnsemble::create() {
     const size_t t = (size_t)N * N;
-    OCEAN_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    OCEAN_CUDA(cudaMalloc(&noise, batch * t * sizeof(float2)));
-    float4** arrs[] = {&h0, &wave, &disp, &deriv, &turb};
-    for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
-    ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4), batch * C);
-    if (!ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
-    rowsA = ws->planeA();
-    rowsB = ws->planeB();
-    OCEAN_CUDA(cudaMalloc(&waveHot, (size_t)batch * C * t * sizeof(float2)));
-    if (rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&h0c, (size_t)batch * C * t * sizeof(float2)));
+    if (const char* e = getenv("OCEAN_ENSEMBLE_LANES")) lanes = atoi(e) <= 1 ? 1 : MAX_LANES;
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
-    for (int i = 0; i < 2; ++i) {
-        OCEAN_CUDA(cudaMalloc(&stateDev[i], batch * sizeof(StateConsts)));
-        OCEAN_CUDA(cudaMalloc(&seedDev[i], batch * sizeof(uint64_t)));
-        OCEAN_CUDA(cudaMalloc(&sumDev[i], (size_t)batch * 3 * sizeof(unsigned long long)));
-        OCEAN_CUDA(cudaMallocHost(&stateHost[i], batch * sizeof(StateConsts)));
-        OCEAN_CUDA(cudaMallocHost(&seedHost[i], batch * sizeof(uint64_t)));
-        OCEAN_CUDA(cudaMallocHost(&sumHost[i], (size_t)batch * 3 * sizeof(unsigned long long)));
-        OCEAN_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
-    }
     OCEAN_CUDA(configure_frame_kernels(N));
-    OCEAN_CUDA(make_cols_maps(N, batch * C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
-
+    for (int l = 0; l < lanes; ++l) {
+        EnsembleLane& L = lane[l];
+        OCEAN_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        OCEAN_CUDA(cudaMalloc(&L.noise, batch * t * sizeof(float2)));
+        float4** arrs[] = {&L.h0, &L.disp, &L.deriv, &L.turb};
+        for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
+        L.ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4), batch * C);
+        if (!L.ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
+        OCEAN_CUDA(cudaMalloc(&L.waveHot, (size_t)batch * C * t * sizeof(float2)));
+        if (rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&L.h0c, (size_t)batch * C * t * sizeof(float2)));
+        OCEAN_CUDA(cudaMalloc(&L.stateDev, batch * sizeof(StateConsts)));
+        OCEAN_CUDA(cudaMalloc(&L.seedDev, batch * sizeof(uint64_t)));
+        OCEAN_CUDA(cudaMalloc(&L.sumDev, (size_t)batch * 3 * sizeof(unsigned long long)));
+        OCEAN_CUDA(cudaMallocHost(&L.stateHost, batch * sizeof(StateConsts)));
+        OCEAN_CUDA(cudaMallocHost(&L.seedHost, batch * sizeof(uint64_t)));
+        OCEAN_CUDA(cudaMallocHost(&L.sumHost, (size_t)batch * 3 * sizeof(unsigned long long)));
+        OCEAN_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+        OCEAN_CUDA(make_cols_maps(N, batch * C, L.ws->planeA(), L.ws->planeB(), L.disp, L.deriv, L.turb, &L.colsMaps));
+    }
     return OCEAN_OK;
 }
 
@@ -712,84 +723,92 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
     ia.N = N; ia.C = C;
     ia.sc = make_spread_consts();
     for (int i = 0; i < C; ++i) ia.casc[i] = make_cascade_consts(cascades[i]);
-    ia.noise = noise; ia.h0 = h0; ia.wave = wave; ia.waveHot = waveHot; ia.h0c = h0c;
     int waveIdx = 0;
-    int pendingBase[2] = {-1, -1}, pendingCount[2] = {0, 0};
+    int pendingBase[MAX_LANES] = {-1, -1}, pendingCount[MAX_LANES] = {0, 0};
     auto drain = [&](int b) {
         if (pendingBase[b] < 0) return cudaSuccess;
-        cudaError_t e = cudaEventSynchronize(done[b]);
+        cudaError_t e = cudaEventSynchronize(lane[b].done);
         if (e != cudaSuccess) return e;
         if (checksums)
-            memcpy(checksums + (size_t)pendingBase[b] * 3, sumHost[b], (size_t)pendingCount[b] * 3 * sizeof(uint64_t));
+            memcpy(checksums + (size_t)pendingBase[b] * 3, lane[b].sumHost, (size_t)pendingCount[b] * 3 * sizeof(uint64_t));
         pendingBase[b] = -1;
         return cudaSuccess;
     };
     for (int base = 0; base < nStates; base += batch, ++waveIdx) {
         const int nb = nStates - base < batch ? nStates - base : batch;
-        const int b = waveIdx & 1;
+        const int b = waveIdx % lanes;
+        EnsembleLane& L = lane[b];
+        cudaStream_t stream = L.stream;
         OCEAN_CUDA(drain(b));
         for (int i = 0; i < nb; ++i) {
             OceanParams p = states[base + i];
             p.textureSize = N;
             int rc = validate_params(p);
             if (rc != OCEAN_OK) return rc;
-            stateHost[b][i] = make_state_consts(p);
-            seedHost[b][i] = seeds ? seeds[base + i] : (uint64_t)(base + i);
+            L.stateHost[i] = make_state_consts(p);
+            L.seedHost[i] = seeds ? seeds[base + i] : (uint64_t)(base + i);
         }
-        OCEAN_CUDA(cudaMemcpyAsync(stateDev[b], stateHost[b], nb * sizeof(StateConsts), cudaMemcpyHostToDevice, stream));
-        OCEAN_CUDA(cudaMemcpyAsync(seedDev[b], seedHost[b], nb * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
-        OCEAN_CUDA(cudaMemsetAsync(sumDev[b], 0, (size_t)nb * 3 * sizeof(unsigned long long), stream));
-        OCEAN_CUDA(launch_noise(seedDev[b], nb, N, noise, stream));
-        ia.nStates = nb; ia.states = stateDev[b];
+        OCEAN_CUDA(cudaMemcpyAsync(L.stateDev, L.stateHost, nb * sizeof(StateConsts), cudaMemcpyHostToDevice, stream));
+        OCEAN_CUDA(cudaMemcpyAsync(L.seedDev, L.seedHost, nb * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+        OCEAN_CUDA(cudaMemsetAsync(L.sumDev, 0, (size_t)nb * 3 * sizeof(unsigned long long), stream));
+        OCEAN_CUDA(launch_noise(L.seedDev, nb, N, L.noise, stream));
+        // waveData (the reference's inspection layout) is not kept by ensembles: the frame reads waveHot
+        ia.noise = L.noise; ia.h0 = L.h0; ia.wave = nullptr; ia.waveHot = L.waveHot; ia.h0c = L.h0c;
+        ia.nStates = nb; ia.states = L.stateDev;
         OCEAN_CUDA(launch_init(ia, stream));
         FrameArgs fa{};
         fa.N = N; fa.layers = nb * C; fa.C = C;
         for (int i = 0; i < C; ++i) fa.dk[i] = ia.casc[i].dk;
-        fa.h0 = h0; fa.waveHot = waveHot; fa.h0c = h0c; fa.rowsA = rowsA; fa.rowsB = rowsB; fa.disp = disp; fa.deriv = deriv; fa.turb = turb;
+        fa.h0 = L.h0; fa.waveHot = L.waveHot; fa.h0c = L.h0c; fa.rowsA = L.ws->planeA(); fa.rowsB = L.ws->planeB();
+        fa.disp = L.disp; fa.deriv = L.deriv; fa.turb = L.turb;
         fa.twiddle = twiddle; fa.time = time;
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
         // a short last wave leaves the upper layers' counters behind: restart the counting per wave
-        ws->rowPasses = ws->colPasses = 0;
-        OCEAN_CUDA(cudaMemsetAsync(ws->counters, 0, (size_t)2 * ws->layers * sizeof(unsigned long long), stream));
-        workspace_stamp(ws, N, true, true, &fa);
-        l2_window(device, ws, &fa);
-        if (frame_fused_available(N, &colsMaps)) {
-            OCEAN_CUDA(launch_frame(fa, &colsMaps, stream, false));  // follows the init kernel: no early start
-            OCEAN_CUDA(launch_checksum(disp, nb, stateFloat4(), sumDev[b] + 0, 3, stream));
-            OCEAN_CUDA(launch_checksum(deriv, nb, stateFloat4(), sumDev[b] + 1, 3, stream));
-            OCEAN_CUDA(launch_checksum(turb, nb, stateFloat4(), sumDev[b] + 2, 3, stream));
+        L.ws->rowPasses = L.ws->colPasses = 0;
+        OCEAN_CUDA(cudaMemsetAsync(L.ws->counters, 0, (size_t)2 * L.ws->layers * sizeof(unsigned long long), stream));
+        workspace_stamp(L.ws, N, true, true, &fa);
+        l2_window(device, L.ws, &fa);
+        if (frame_fused_available(N, &L.colsMaps)) {
+            OCEAN_CUDA(launch_frame(fa, &L.colsMaps, stream, false));  // follows the init kernel: no early start
+            OCEAN_CUDA(launch_checksum(L.disp, nb, stateFloat4(), L.sumDev + 0, 3, stream));
+            OCEAN_CUDA(launch_checksum(L.deriv, nb, stateFloat4(), L.sumDev + 1, 3, stream));
+            OCEAN_CUDA(launch_checksum(L.turb, nb, stateFloat4(), L.sumDev + 2, 3, stream));
         } else {
-            fa.checksums = sumDev[b];  // reduced inside the column pass: the outputs are not read back
+            fa.checksums = L.sumDev;  // reduced inside the column pass: the outputs are not read back
             OCEAN_CUDA(launch_rows(fa, stream, false));
-            OCEAN_CUDA(launch_cols(fa, &colsMaps, stream));
+            OCEAN_CUDA(launch_cols(fa, &L.colsMaps, stream));
         }
-        OCEAN_CUDA(cudaMemcpyAsync(sumHost[b], sumDev[b], (size_t)nb * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
-        OCEAN_CUDA(cudaEventRecord(done[b], stream));
+        OCEAN_CUDA(cudaMemcpyAsync(L.sumHost, L.sumDev, (size_t)nb * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+        OCEAN_CUDA(cudaEventRecord(L.done, stream));
         pendingBase[b] = base; pendingCount[b] = nb;
         lastCount = nb;
+        lastLane = b;
     }
-    OCEAN_CUDA(drain(0));
-    OCEAN_CUDA(drain(1));
-    OCEAN_CUDA(cudaStreamSynchronize(stream));
+    for (int b = 0; b < lanes; ++b) OCEAN_CUDA(drain(b));
+    for (int b = 0; b < lanes; ++b) OCEAN_CUDA(cudaStreamSynchronize(lane[b].stream));
     return OCEAN_OK;
 }
 
 void OceanEnsemble::destroy() {
-    if (stream) cudaStreamSynchronize(stream);
-    workspace_release(ws);
-    ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev[0], stateDev[1], seedDev[0], seedDev[1], sumDev[0], sumDev[1]};
-    for (void* p : dev)
-        if (p) cudaFree(p);
-    for (int i = 0; i < 2; ++i) {
-        if (stateHost[i]) cudaFreeHost(stateHost[i]);
-        if (seedHost[i]) cudaFreeHost(seedHost[i]);
-        if (sumHost[i]) cudaFreeHost(sumHost[i]);
-        if (done[i]) cudaEventDestroy(done[i]);
+    for (int l = 0; l < MAX_LANES; ++l) {
+        EnsembleLane& L = lane[l];
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        workspace_release(L.ws);
+        L.ws = nullptr;
+        void* dev[] = {L.noise, L.h0, L.waveHot, L.h0c, L.disp, L.deriv, L.turb, L.stateDev, L.seedDev, L.sumDev};
+        for (void* p : dev)
+            if (p) cudaFree(p);
+        if (L.stateHost) cudaFreeHost(L.stateHost);
+        if (L.seedHost) cudaFreeHost(L.seedHost);
+        if (L.sumHost) cudaFreeHost(L.sumHost);
+        if (L.done) cudaEventDestroy(L.done);
+        if (L.stream) cudaStreamDestroy(L.stream);
+        L = EnsembleLane{};
     }
-    if (stream) cudaStreamDestroy(stream);
+    if (twiddle) cudaFree(twiddle);
+    twiddle = nullptr;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1117,12 +1136,13 @@ int ocean_ensemble_run(OceanEnsemble* e, const OceanParams* states, const uint64
 
 static int ens_pick(OceanEnsemble* e, int which, void** p, size_t* bytes) {
     const size_t all = (size_t)e->batch * e->stateFloat4() * sizeof(float4);
+    const EnsembleLane& L = e->lane[e->lastLane];
     switch (which) {
-        case OCEAN_DISPLACEMENT: *p = e->disp; break;
-        case OCEAN_DERIVATIVES: *p = e->deriv; break;
-        case OCEAN_TURBULENCE: *p = e->turb; break;
-        case OCEAN_INITIAL_SPECTRUM: *p = e->h0; break;
-        case OCEAN_WAVES_DATA: *p = e->wave; break;
+        case OCEAN_DISPLACEMENT: *p = L.disp; break;
+        case OCEAN_DERIVATIVES: *p = L.deriv; break;
+        case OCEAN_TURBULENCE: *p = L.turb; break;
+        case OCEAN_INITIAL_SPECTRUM: *p = L.h0; break;
+        case OCEAN_WAVES_DATA: return fail(OCEAN_ERR_INVALID_ARGUMENT, "ensembles do not keep waveData (inspect it on a stand-alone ocean)");
         default: return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown array id %d", which);
     }
     *bytes = all;
@@ -1142,7 +1162,7 @@ int ocean_ensemble_copy_output(OceanEnsemble* e, int which, int slot, float* hos
     int rc = ens_pick(e, which, &p, &bytes);
     if (rc != OCEAN_OK) return rc;
     const size_t per = e->stateFloat4() * sizeof(float4);
-    OCEAN_CUDA(cudaStreamSynchronize(e->stream));
+    OCEAN_CUDA(cudaStreamSynchronize(e->lane[e->lastLane].stream));
     OCEAN_CUDA(cudaMemcpy(host, (const char*)p + (size_t)slot * per, per, cudaMemcpyDeviceToHost));
     return OCEAN_OK;
 }

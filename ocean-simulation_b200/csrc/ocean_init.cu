@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
     const Texel tp = initial_spectrum_texel(kx, kz, rd, sc, cc, __ldg(&noise[(size_t)y * N + x]));
     if (m == p) {
         a.h0[p] = make_float4(tp.h.x, tp.h.y, tp.h.x, -tp.h.y);  // IS:141
-        a.wave[p] = tp.wave;
+        if (a.wave) a.wave[p] = tp.wave;
         a.waveHot[p] = make_float2(tp.wave.y, tp.wave.w);
         if (a.h0c) a.h0c[p] = tp.h;
         return;
@@ -131,8 +131,10 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
     const Texel tm = initial_spectrum_texel(kxm, kzm, rd, sc, cc, __ldg(&noise[(size_t)my * N + mx]));
     a.h0[p] = make_float4(tp.h.x, tp.h.y, tm.h.x, -tm.h.y);
     a.h0[m] = make_float4(tm.h.x, tm.h.y, tp.h.x, -tp.h.y);
-    a.wave[p] = tp.wave;
-    a.wave[m] = tm.wave;
+    if (a.wave) {
+        a.wave[p] = tp.wave;
+        a.wave[m] = tm.wave;
+    }
     a.waveHot[p] = make_float2(tp.wave.y, tp.wave.w);
     a.waveHot[m] = make_float2(tm.wave.y, tm.wave.w);
     if (a.h0c) {

@@ -46,7 +46,7 @@ struct InitArgs {
     const StateConsts* states;         // device, nStates entries
     const float2* noise;               // device, [state][y][x]
     float4* h0;                        // device, [state*C + cascade][y][x]
-    float4* wave;                      // (kx, 1/|k|, kz, omega): the reference's waveData layout (inspection / parity)
+    float4* wave;                      // (kx, 1/|k|, kz, omega): the reference's waveData layout (inspection / parity); nullptr: not kept (ensembles)
     float2* waveHot;                   // (1/|k|, omega): what the frame kernels read; kx, kz are recomputed as n*dk
     float2* h0c;                       // h0(k) alone: the pair-row kernel reads it at k and at -k instead of the 16-byte packing
 };
