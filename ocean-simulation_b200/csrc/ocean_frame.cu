@@ -171,6 +171,11 @@ __device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned
 #ifndef OCEAN_ROWS_WAVE_REGS
 #define OCEAN_ROWS_WAVE_REGS 1
 #endif
+// Sensitivity experiments (variants/build_variants.py; results are WRONG, only the timing is of interest):
+// 1: row pass reads L2-resident rows, 2: column pass stores nothing, 4: no turbulence load, 8: row pass stores nothing
+#ifndef OCEAN_EXP
+#define OCEAN_EXP 0
+#endif
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
@@ -234,9 +239,43 @@ __device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
 #define OCEAN_ROWS_FAST_SINCOS 0
 #endif
 
+// CalculateTimeDependentComplexAmplitudesAndDerivatives TD:20-47 for one texel: h0 = (h0(k), conj h0(-k)),
+// wv = (1/|k|, omega); returns the eight derived spectra in the packed pair layout.
+__device__ __forceinline__ void evolve_texel(const float4 h0, const float2 wv, const float kx, const float kz, const float time,
+                                             C2& pa, C2& pb) {
+        const float ik = wv.x;
+        // TD:23-26
+        float sn, cs;
+#if OCEAN_ROWS_FAST_SINCOS
+        phase_sincos(wv.y * time, sn, cs);
+#else
+        sincosf(wv.y * time, &sn, &cs);
+#endif
+        const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
+        const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
+        const float ihx = -hy, ihy = hx;
+        // TD:29-40
+        const float ydx_x = ihx * kx, ydx_y = ihy * kx;
+        const float ydz_x = ihx * kz, ydz_y = ihy * kz;
+        const float X_x = ydx_x * ik, X_y = ydx_y * ik;
+        const float Z_x = ydz_x * ik, Z_y = ydz_y * ik;
+        const float ax = -hx * ik, ay = -hy * ik;
+        const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
+        const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
+        const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
+        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz), each held as
+        // re = (re of first, re of second), im = (im of first, im of second)
+        pa = C2{pk2(X_x - Z_y, hx - zdx_y), pk2(X_y + Z_x, hy + zdx_x)};
+        pb = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
+}
+
 // ---------------------------------------------------------------------------------------------
 // workspace stores of the row pass
 __device__ __forceinline__ void ws_store(float4* p, const C2& v) {
+#if OCEAN_EXP & 8
+    if (v.re == 0x123456789abcdefull) c2_store(p, v);  // sensitivity: (practically) never stores
+    return;
+#endif
 #if OCEAN_L2_HINTS & 4
     c2_store_hint(p, v, L2_EVICT_LAST);
 #else
@@ -260,8 +299,13 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     size_t line = (size_t)blockIdx.x * R + row;  // = layer*N + y
     const bool active = line < totalRows;
     if (!active) line = totalRows - 1;  // keep every thread in the barriers; results are dropped
+#if OCEAN_EXP & 1  // sensitivity: every CTA reads the same 8 rows (L2 hits instead of HBM)
+    const float4* __restrict__ H = a.h0 + (line & 7) * N;
+    const float2* __restrict__ Wd = a.waveHot + (line & 7) * N;
+#else
     const float4* __restrict__ H = a.h0 + line * N;
     const float2* __restrict__ Wd = a.waveHot + line * N;
+#endif
     pdl_trigger();
     TRACE(0, blockIdx.x, 0);
 
@@ -302,30 +346,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         const float2 wv = ws[row * N + x];
 #endif
         const float kx = (float)(x - N / 2) * dk;  // IS:111 (waveData.x)
-        const float ik = wv.x;
-        // TD:23-26
-        float sn, cs;
-#if OCEAN_ROWS_FAST_SINCOS
-        phase_sincos(wv.y * time, sn, cs);
-#else
-        sincosf(wv.y * time, &sn, &cs);
-#endif
-        const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
-        const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
-        const float ihx = -hy, ihy = hx;
-        // TD:29-40
-        const float ydx_x = ihx * kx, ydx_y = ihy * kx;
-        const float ydz_x = ihx * kz, ydz_y = ihy * kz;
-        const float X_x = ydx_x * ik, X_y = ydx_y * ik;
-        const float Z_x = ydz_x * ik, Z_y = ydz_y * ik;
-        const float ax = -hx * ik, ay = -hy * ik;
-        const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
-        const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
-        const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
-        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz), each held as
-        // re = (re of first, re of second), im = (im of first, im of second)
-        pa[j] = C2{pk2(X_x - Z_y, hx - zdx_y), pk2(X_y + Z_x, hy + zdx_x)};
-        pb[j] = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
+        evolve_texel(h0, wv, kx, kz, time, pa[j], pb[j]);
     }
 
     TRACE(0, blockIdx.x, 2);
@@ -725,13 +746,16 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             }
         };
         // pair B travels with the tile's incoming turbulence texels (RF:28), which land in bufT
-        const bool needFoam = a.zeroFoam == 0;
+        const bool needFoam = a.zeroFoam == 0 && !(OCEAN_EXP & 4);  // sensitivity bit 4: no turbulence load
         auto loadB = [&](int tile) {
             mbar_arrive_expect_tx(&bars[1], Cfg::TILE_ELEMS * 16 * (needFoam ? 2 : 1));
             load(&maps.b, bufB, &bars[1], tile);
             if (needFoam) load(&maps.turb, bufT, &bars[1], tile);
         };
         auto store = [&](const CUtensorMap* map, const float4* buf, int tile) {
+#if OCEAN_EXP & 2  // sensitivity: no output stores
+            return;
+#endif
             int c0, c1;
             coords(tile, c0, c1);
 #pragma unroll
@@ -808,7 +832,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     const int xw = threadIdx.x & (W - 1);
     const int tid = threadIdx.x / W;
     const float lambda = a.lambda, decay = a.foamDecay;
-    const bool zeroFoam = a.zeroFoam != 0;
+    const bool zeroFoam = a.zeroFoam != 0 || (OCEAN_EXP & 4);
     uint32_t parity = 0;
     for (int tile = blockIdx.x; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
         const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;

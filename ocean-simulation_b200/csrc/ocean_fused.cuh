@@ -181,29 +181,7 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
     }
 }
 
-// TD:20-47 for one texel: h0 = (h0(k), conj h0(-k)), wv = (1/|k|, w).  Outputs the two packed pairs
-// pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz), each as re = (re of first, re of second), im likewise.
-__device__ __forceinline__ void evolve_texel(const float4 h0, const float2 wv, const float kx, const float kz, const float time,
-                                             C2& pa, C2& pb) {
-    const float ik = wv.x;
-    float sn, cs;
-    sincosf(wv.y * time, &sn, &cs);  // TD:23-25
-    const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);  // TD:26
-    const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
-    const float ihx = -hy, ihy = hx;
-    // TD:29-40
-    const float ydx_x = ihx * kx, ydx_y = ihy * kx;
-    const float ydz_x = ihx * kz, ydz_y = ihy * kz;
-    const float X_x = ydx_x * ik, X_y = ydx_y * ik;
-    const float Z_x = ydz_x * ik, Z_y = ydz_y * ik;
-    const float ax = -hx * ik, ay = -hy * ik;
-    const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
-    const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
-    const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
-    // TD:42-45: A + iB packing
-    pa = C2{pk2(X_x - Z_y, hx - zdx_y), pk2(X_y + Z_x, hy + zdx_x)};
-    pb = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
-}
+// (evolve_texel: ocean_frame.cu)
 
 template <int N>
 __global__ void __launch_bounds__(FusedCfg<N>::THREADS, 2)

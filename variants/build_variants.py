@@ -7,10 +7,9 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
-    "h06": ["-DOCEAN_COLS_L2_HINTS=6"],
-    "h07": ["-DOCEAN_COLS_L2_HINTS=7"],
-    "h14": ["-DOCEAN_COLS_L2_HINTS=14"],
-    "h15": ["-DOCEAN_COLS_L2_HINTS=15"],
+    "x04_no_turb_load": ["-DOCEAN_EXP=4"],
+    "x16_2cta": ["-DOCEAN_EXP=16", "-DOCEAN_COLS_TMA_CTAS_PER_SM=2"],
+    "x16_3cta": ["-DOCEAN_EXP=16", "-DOCEAN_COLS_TMA_CTAS_PER_SM=3"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
@@ -21,7 +20,7 @@ if __name__ == "__main__":
         cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
-        info = re.findall(r"ocean_(rows|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
+        info = re.findall(r"ocean_(rows|rows_seq|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
         others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o", "ocean_surface.o")]
         subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", os.path.join(HERE, "lib_%s.so" % n), obj] + others)
         os.remove(obj)
