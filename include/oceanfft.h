@@ -219,7 +219,10 @@ int ocean_ensemble_run(OceanEnsemble* e, const OceanParams* states, const uint64
 /* Device pointers of the pooled arrays of the last wave ([batch*C][N][N][4]): the three outputs and
  * OCEAN_INITIAL_SPECTRUM.  Waves alternate between two sets of pooled buffers (two lanes, so that the
  * ALU-bound spectrum kernels of one wave overlap the memory-bound frame of the other); the pointers are
- * those of the lane that ran the last wave.  OCEAN_WAVES_DATA is not kept by ensembles. */
+ * those of the lane that ran the last wave.  OCEAN_WAVES_DATA is not kept by ensembles, and with
+ * OCEAN_ENSEMBLE_FUSED_INIT=1 in the environment at create time (initial spectrum fused into the row pass: no
+ * pooled h0 / waveHot buffers, 40 B per texel-cascade less memory, ~9 % slower on B200) neither is
+ * OCEAN_INITIAL_SPECTRUM. */
 int ocean_ensemble_get_output(OceanEnsemble* e, int which, void** devPtr, size_t* bytes);
 int ocean_ensemble_copy_output(OceanEnsemble* e, int which, int slot, float* host /* C*N*N*4 */);
 

@@ -22,7 +22,7 @@ UNITS = {
     "ocean_surface.cu": ["-fmad=false"],  # sampler / shading arithmetic: bit-comparable with the fp32 oracle
     "ocean_host.cu": [],
 }
-HEADERS = ["ocean_internal.h", "ocean_fft.cuh", "ocean_tma.cuh", "ocean_fused.cuh", "../../include/oceanfft.h", "../../include/ocean_noise.h"]
+HEADERS = ["ocean_internal.h", "ocean_fft.cuh", "ocean_tma.cuh", "ocean_fused.cuh", "ocean_evolve.cuh", "ocean_spectrum.cuh", "../../include/oceanfft.h", "../../include/ocean_noise.h"]
 
 
 def _nvcc():

@@ -20,6 +20,7 @@
 #include "ocean_fft.cuh"
 #include "ocean_internal.h"
 #include "ocean_tma.cuh"
+#include "ocean_evolve.cuh"
 
 namespace ocean {
 
@@ -172,7 +173,8 @@ __device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned
 #define OCEAN_ROWS_WAVE_REGS 1
 #endif
 // Sensitivity experiments (variants/build_variants.py; results are WRONG, only the timing is of interest):
-// 1: row pass reads L2-resident rows, 2: column pass stores nothing, 4: no turbulence load, 8: row pass stores nothing
+// 1: row pass reads L2-resident rows, 2: column pass stores nothing, 4: no turbulence load, 8: row pass stores nothing,
+// 32: no sincos in the row pass, 64: both kernels only wait for / publish their counters (launch + hand-off floor), 128: both kernels return at once
 #ifndef OCEAN_EXP
 #define OCEAN_EXP 0
 #endif
@@ -199,75 +201,6 @@ template <int N> struct ColCfg {
     static constexpr int MINB = (N == 512) ? OCEAN_COLS512_MINB : 1;
     using FFT = LineFFT<N, W, true, DB>;
 };
-
-// sin and cos of a phase: 3-term Cody-Waite reduction to [-pi/4, pi/4] (the constants CUDA's own
-// sincosf uses on its fast path, valid below 105615 rad) followed by the SFU approximations, whose
-// absolute error (~4e-7) is of the order of the transform's own rounding.  Larger phases take the
-// library path.
-__device__ __noinline__ float2 phase_sincos_large(float x) {
-    float sn, cs;
-    sincosf(x, &sn, &cs);
-    return make_float2(sn, cs);
-}
-__device__ __forceinline__ void phase_sincos(float x, float& sn, float& cs) {
-    if (fabsf(x) > 105615.0f) {
-        const float2 r = phase_sincos_large(x);
-        sn = r.x;
-        cs = r.y;
-        return;
-    }
-    const float magic = 12582912.0f;  // 1.5 * 2^23: adding it rounds to the nearest integer
-    const float qf = __fmaf_rn(x, 0.636619772f, magic);
-    const int iq = __float_as_int(qf);  // low bits = round(x * 2/pi)
-    const float q = qf - magic;
-    float r = __fmaf_rn(q, -1.57079601e+00f, x);
-    r = __fmaf_rn(q, -3.13916473e-07f, r);
-    r = __fmaf_rn(q, -5.39030253e-15f, r);
-    const float s0 = __sinf(r), c0 = __cosf(r);
-    const bool odd = iq & 1;
-    const float sv = odd ? c0 : s0, cv = odd ? s0 : c0;
-    sn = __int_as_float(__float_as_int(sv) ^ ((iq & 2) << 30));
-    cs = __int_as_float(__float_as_int(cv) ^ (((iq + 1) & 2) << 30));
-}
-
-// measured on B200 at 4 x 512^2: the SFU path executes 18% fewer instructions but the frame is not
-// issue-bound (27.2 us vs 26.9 us with the library sincosf), so the precise path stays the default
-#ifndef OCEAN_ROWS_DUAL_FFT
-#define OCEAN_ROWS_DUAL_FFT 0
-#endif
-#ifndef OCEAN_ROWS_FAST_SINCOS
-#define OCEAN_ROWS_FAST_SINCOS 0
-#endif
-
-// CalculateTimeDependentComplexAmplitudesAndDerivatives TD:20-47 for one texel: h0 = (h0(k), conj h0(-k)),
-// wv = (1/|k|, omega); returns the eight derived spectra in the packed pair layout.
-__device__ __forceinline__ void evolve_texel(const float4 h0, const float2 wv, const float kx, const float kz, const float time,
-                                             C2& pa, C2& pb) {
-        const float ik = wv.x;
-        // TD:23-26
-        float sn, cs;
-#if OCEAN_ROWS_FAST_SINCOS
-        phase_sincos(wv.y * time, sn, cs);
-#else
-        sincosf(wv.y * time, &sn, &cs);
-#endif
-        const float hx = (h0.x * cs - h0.y * sn) + (h0.z * cs + h0.w * sn);
-        const float hy = (h0.x * sn + h0.y * cs) + (h0.w * cs - h0.z * sn);
-        const float ihx = -hy, ihy = hx;
-        // TD:29-40
-        const float ydx_x = ihx * kx, ydx_y = ihy * kx;
-        const float ydz_x = ihx * kz, ydz_y = ihy * kz;
-        const float X_x = ydx_x * ik, X_y = ydx_y * ik;
-        const float Z_x = ydz_x * ik, Z_y = ydz_y * ik;
-        const float ax = -hx * ik, ay = -hy * ik;
-        const float xdx_x = ax * kx * kx, xdx_y = ay * kx * kx;
-        const float zdz_x = ax * kz * kz, zdz_y = ay * kz * kz;
-        const float zdx_x = ax * kx * kz, zdx_y = ay * kx * kz;
-        // TD:42-45: A + iB packing; pa = (DxDz, DyDxz), pb = (DyxDyz, DxxDzz), each held as
-        // re = (re of first, re of second), im = (im of first, im of second)
-        pa = C2{pk2(X_x - Z_y, hx - zdx_y), pk2(X_y + Z_x, hy + zdx_x)};
-        pb = C2{pk2(ydx_x - ydz_y, xdx_x - zdz_y), pk2(ydx_y + ydz_x, xdx_y + zdz_x)};
-}
 
 // ---------------------------------------------------------------------------------------------
 // workspace stores of the row pass
@@ -308,6 +241,17 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
 #endif
     pdl_trigger();
     TRACE(0, blockIdx.x, 0);
+#if OCEAN_EXP & 128  // sensitivity: pure launch floor
+    return;
+#endif
+#if OCEAN_EXP & 64  // sensitivity: launch / dispatch / counter floor -- publish and leave
+    if (threadIdx.x == 0) {
+        spin_until_ge(a.colsDone + (size_t)blockIdx.x * R / N, a.colsTarget);
+        __threadfence();
+        atomicAdd(a.rowsDone + (size_t)blockIdx.x * R / N, (unsigned long long)R);
+    }
+    return;
+#endif
 
     // Stage the whole row: 16 asynchronous copies per thread are in flight before any arithmetic.
     // Element x lands in the slot exchange 0 will later use for it, and thread `tid` only ever
@@ -670,6 +614,9 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 #endif
 // persistent grid = SMs x this many CTAs (capped by occupancy).  Fewer column CTAs per SM leave room
 // for row CTAs of the NEXT frame to run in the shadow of this (HBM-bound) kernel.
+#ifndef OCEAN_COLS_EARLY_PRODUCER
+#define OCEAN_COLS_EARLY_PRODUCER 1
+#endif
 #ifndef OCEAN_COLS_TMA_CTAS_PER_SM
 #define OCEAN_COLS_TMA_CTAS_PER_SM 2
 #endif
@@ -706,6 +653,23 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 
     pdl_trigger();
     TRACE(1, blockIdx.x, 0);
+#if OCEAN_COLS_EARLY_PRODUCER
+    // The producer lane initialises the barriers and goes straight to its first tile's loads; the compute
+    // warps copy the (immutable) twiddle table meanwhile and meet on their own named barrier, so the table's
+    // L2 round trip and the tile's TMA round trip overlap instead of adding up at the head of every CTA.
+    if (threadIdx.x == Cfg::COMPUTE) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], Cfg::COMPUTE);
+        mbar_init(&bars[3], Cfg::COMPUTE);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x < Cfg::COMPUTE) {
+        for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::COMPUTE) twS[i] = __ldg(&a.twiddle[i]);
+        FFT::barrier();
+    }
+#else
     if (threadIdx.x == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -716,6 +680,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     // the twiddle table is immutable: copying it may overlap the previous kernel
     for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twS[i] = __ldg(&a.twiddle[i]);
     __syncthreads();
+#endif
     // No griddepcontrol.wait here: the producer gates every tile on its layer's row counter instead.
     // A counter can only reach the target after row CTAs of THIS frame passed their own
     // griddepcontrol.wait, i.e. after everything earlier in the stream (the previous column pass
@@ -729,6 +694,18 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         c1 = layer * N;
     };
 
+#if OCEAN_EXP & 128
+    return;
+#endif
+#if OCEAN_EXP & 64  // sensitivity: launch / dispatch / counter floor -- wait for the rows, publish and leave
+    if (threadIdx.x == 0)
+        for (int tile = blockIdx.x; tile < totalTiles; tile += gridDim.x) {
+            spin_until_ge(a.rowsDone + tile / TILES_PER_LAYER, a.rowsTarget);
+            __threadfence();
+            atomicAdd(a.colsDone + tile / TILES_PER_LAYER, (unsigned long long)W);
+        }
+    return;
+#endif
     if (threadIdx.x >= Cfg::COMPUTE) {
         // ---------------- producer warp ----------------
         if (threadIdx.x != Cfg::COMPUTE) return;

@@ -677,6 +677,10 @@ struct OceanEnsemble {
     static constexpr int MAX_LANES = 2;
     int device = 0, N = 0, C = 0, batch = 0;
     int lanes = MAX_LANES;
+    // OCEAN_ENSEMBLE_FUSED_INIT=1: initial spectrum fused into the row pass (ocean_rows_from_noise_kernel, SURVEY 8f
+    // N4); h0 / waveHot are never materialised (40 B per texel-cascade less pooled memory).  Off by default: the
+    // spectrum is ALU-bound and the separate kernels are ~9 % faster on B200 (ocean_init.cu).
+    bool fusedInit = false;
     OceanCascade cascades[OCEAN_MAX_CASCADES]{};
     EnsembleLane lane[MAX_LANES];
     float2* twiddle = nullptr;
@@ -692,6 +696,7 @@ struct OceanEnsemble {
 int OceanEnsemble::create() {
     const size_t t = (size_t)N * N;
     if (const char* e = getenv("OCEAN_ENSEMBLE_LANES")) lanes = atoi(e) <= 1 ? 1 : MAX_LANES;
+    if (const char* e = getenv("OCEAN_ENSEMBLE_FUSED_INIT")) fusedInit = rows_from_noise_available(N) && atoi(e) != 0;
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
@@ -700,12 +705,13 @@ int OceanEnsemble::create() {
         EnsembleLane& L = lane[l];
         OCEAN_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
         OCEAN_CUDA(cudaMalloc(&L.noise, batch * t * sizeof(float2)));
-        float4** arrs[] = {&L.h0, &L.disp, &L.deriv, &L.turb};
+        float4** arrs[] = {&L.disp, &L.deriv, &L.turb};
         for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
+        if (!fusedInit) OCEAN_CUDA(cudaMalloc(&L.h0, (size_t)batch * C * t * sizeof(float4)));
         L.ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4), batch * C);
         if (!L.ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
-        OCEAN_CUDA(cudaMalloc(&L.waveHot, (size_t)batch * C * t * sizeof(float2)));
-        if (rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&L.h0c, (size_t)batch * C * t * sizeof(float2)));
+        if (!fusedInit) OCEAN_CUDA(cudaMalloc(&L.waveHot, (size_t)batch * C * t * sizeof(float2)));
+        if (!fusedInit && rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&L.h0c, (size_t)batch * C * t * sizeof(float2)));
         OCEAN_CUDA(cudaMalloc(&L.stateDev, batch * sizeof(StateConsts)));
         OCEAN_CUDA(cudaMalloc(&L.seedDev, batch * sizeof(uint64_t)));
         OCEAN_CUDA(cudaMalloc(&L.sumDev, (size_t)batch * 3 * sizeof(unsigned long long)));
@@ -755,7 +761,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         // waveData (the reference's inspection layout) is not kept by ensembles: the frame reads waveHot
         ia.noise = L.noise; ia.h0 = L.h0; ia.wave = nullptr; ia.waveHot = L.waveHot; ia.h0c = L.h0c;
         ia.nStates = nb; ia.states = L.stateDev;
-        OCEAN_CUDA(launch_init(ia, stream));
+        if (!fusedInit) OCEAN_CUDA(launch_init(ia, stream));
         FrameArgs fa{};
         fa.N = N; fa.layers = nb * C; fa.C = C;
         for (int i = 0; i < C; ++i) fa.dk[i] = ia.casc[i].dk;
@@ -770,7 +776,11 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         OCEAN_CUDA(cudaMemsetAsync(L.ws->counters, 0, (size_t)2 * L.ws->layers * sizeof(unsigned long long), stream));
         workspace_stamp(L.ws, N, true, true, &fa);
         l2_window(device, L.ws, &fa);
-        if (frame_fused_available(N, &L.colsMaps)) {
+        if (fusedInit) {
+            fa.checksums = L.sumDev;  // reduced inside the column pass: the outputs are not read back
+            OCEAN_CUDA(launch_rows_from_noise(ia, fa, stream));
+            OCEAN_CUDA(launch_cols(fa, &L.colsMaps, stream));
+        } else if (frame_fused_available(N, &L.colsMaps)) {
             OCEAN_CUDA(launch_frame(fa, &L.colsMaps, stream, false));  // follows the init kernel: no early start
             OCEAN_CUDA(launch_checksum(L.disp, nb, stateFloat4(), L.sumDev + 0, 3, stream));
             OCEAN_CUDA(launch_checksum(L.deriv, nb, stateFloat4(), L.sumDev + 1, 3, stream));
@@ -1141,7 +1151,10 @@ static int ens_pick(OceanEnsemble* e, int which, void** p, size_t* bytes) {
         case OCEAN_DISPLACEMENT: *p = L.disp; break;
         case OCEAN_DERIVATIVES: *p = L.deriv; break;
         case OCEAN_TURBULENCE: *p = L.turb; break;
-        case OCEAN_INITIAL_SPECTRUM: *p = L.h0; break;
+        case OCEAN_INITIAL_SPECTRUM:
+            if (!L.h0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "this ensemble fuses the spectrum into the row pass (OCEAN_ENSEMBLE_FUSED_INIT=1) and keeps no h0");
+            *p = L.h0;
+            break;
         case OCEAN_WAVES_DATA: return fail(OCEAN_ERR_INVALID_ARGUMENT, "ensembles do not keep waveData (inspect it on a stand-alone ocean)");
         default: return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown array id %d", which);
     }

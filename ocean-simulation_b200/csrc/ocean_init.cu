@@ -11,6 +11,9 @@
 // so the amplitude is never computed twice and the reference's in-place second pass disappears.
 #include "ocean_internal.h"
 #include "../../include/ocean_noise.h"
+#include "ocean_spectrum.cuh"
+#include "ocean_evolve.cuh"
+#include "ocean_tma.cuh"
 
 namespace ocean {
 
@@ -24,81 +27,6 @@ __global__ void ocean_noise_kernel(const uint64_t* __restrict__ seeds, int N, fl
     v.x = ocean_noise_texel(seed, (uint32_t)N, (uint32_t)x, (uint32_t)y, 0u);
     v.y = ocean_noise_texel(seed, (uint32_t)N, (uint32_t)x, (uint32_t)y, 1u);
     noise[((size_t)st * N + y) * N + x] = v;
-}
-
-struct Texel {
-    float2 h;     // h0(k)
-    float4 wave;  // (kx, 1/|k|, kz, omega)
-};
-
-// Everything in IS:99-129 that depends on |k| only.  A texel and its mirror have the same |k| (kx and kz
-// change sign, or stay put on the x = 0 / y = 0 Nyquist lines), so a thread evaluates this once per pair.
-struct Radial {
-    bool inBand;         // IS:114
-    float kMag, w;       // |k|, omega(k)
-    float twoTmaJonswap; // (2 * tma) * jonswap: the head of the product at IS:120
-    float s, nf;         // spread exponent and its normalisation  IS:60-74
-    float fade, dwdk;    // IS:95-97, IS:87-91
-};
-
-__device__ __forceinline__ Radial initial_spectrum_radial(float kx, float kz, const StateConsts& st, const CascadeConsts& cc,
-                                                          const SpreadConsts& sc) {
-    Radial r;
-    const float kMag = sqrtf(kx * kx + kz * kz);          // length()  IS:112
-    r.kMag = kMag;
-    r.inBand = kMag >= cc.cutoffLow && kMag <= cc.cutoffHigh;  // IS:114
-    if (!r.inBand) return r;
-    const float g = st.gravity, D = st.depth, wp = st.peakOmega;
-    const float w = sqrtf(g * kMag);                  // IS:33-35
-    r.w = w;
-    // TMACorrection IS:38-43
-    const float wh = w * st.sqrtDepthOverG;
-    float tma;
-    if (wh <= 1.0f) tma = 0.5f * wh * wh;
-    else if (wh < 2.0f) tma = 1.0f - 0.5f * (2.0f - wh) * (2.0f - wh);
-    else tma = 1.0f;
-    // JONSWAP IS:47-56
-    const float sigma = w <= wp ? 0.07f : 0.09f;
-    const float d = w - wp;
-    const float rr = expf(-(d * d) / (2.0f * sigma * sigma * wp * wp));
-    const float jonswap = st.alpha * g * g / powf(w, 5.0f) * expf(-1.25f * powf(wp / w, 4.0f)) * powf(3.3f, rr);
-    r.twoTmaJonswap = 2.0f * tma * jonswap;
-    // SpreadPower IS:60-66
-    float sp;
-    if (w < 1.05f * wp) sp = 6.97f * powf(fabsf(w / wp), 4.06f);
-    else sp = 9.77f * powf(fabsf(w / wp), st.mu);
-    // exponent of DirectionalSpread IS:78-84 with NormalizationFactor IS:69-74
-    const float s = sp + 16.0f * tanhf(w / wp) * cc.swell * cc.swell;
-    const float s2 = s * s, s3 = s2 * s;
-    r.s = s;
-    if (s <= 0.4f) r.nf = 0.09f * s3 + sc.c2 * s2 + sc.c1 * s + sc.c0;
-    else r.nf = sqrtf(s) / sc.twoSqrtPi + 1.0f / (16.0f * sqrtf(sc.pi * s));
-    // ShortWavesFade IS:95-97
-    r.fade = expf(-cc.fade * cc.fade * kMag * kMag);
-    // FrequencyDerivative IS:87-91
-    const float th = tanhf(fminf(kMag * D, 20.0f));
-    const float ch = coshf(kMag * D);
-    r.dwdk = g * (D * kMag / ch / ch + th) / (w * 2.0f);
-    return r;
-}
-
-// The direction-dependent rest of IS:99-129 for one texel (helpers IS:33-97 inlined, state scalars hoisted)
-__device__ __forceinline__ Texel initial_spectrum_texel(float kx, float kz, const Radial& rd, const StateConsts& st,
-                                                        const CascadeConsts& cc, float2 xi) {
-    Texel r;
-    if (rd.inBand) {
-        const float k = cc.dk;
-        const float theta = atan2f(kz, kx);               // IS:115
-        const float spread = rd.nf * powf(fabsf(cosf(0.5f * (theta - st.windTheta))), 2.0f * rd.s);  // IS:78-84
-        // IS:120
-        const float amp = sqrtf(rd.twoTmaJonswap * spread * rd.fade * rd.dwdk / rd.kMag * k * k);
-        r.h = make_float2(xi.x / 2.0f * amp, xi.y / 2.0f * amp);
-        r.wave = make_float4(kx, 1.0f / rd.kMag, kz, rd.w);  // IS:123
-    } else {
-        r.h = make_float2(0.0f, 0.0f);                 // IS:125
-        r.wave = make_float4(kx, 1.0f, kz, 0.0f);      // IS:126
-    }
-    return r;
 }
 
 __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs a) {
@@ -140,6 +68,152 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
     if (a.h0c) {
         a.h0c[p] = tp.h;
         a.h0c[m] = tm.h;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Spectrum-to-rows kernel (initial spectrum fused into the first FFT pass).  For an ocean
+// that is evolved once from a fresh spectrum (ensembles, BASELINE config 5; a live parameter change) h0 and
+// waveData never need to exist in memory: one CTA owns the mirrored row pair (y, N - y) of one layer
+// (rows 0 and N/2, which mirror onto themselves, share a CTA), evaluates IS:99-143 for it into shared
+// memory -- the |k|-only factors once per mirrored texel pair, exactly as ocean_init_spectrum_kernel does, so
+// h0 is bit-identical to the stand-alone kernel's -- then runs TD:20-47 and the x-direction inverse FFT of
+// the two rows and writes the workspace planes the column pass reads.  Per texel-cascade it reads 8 B of
+// noise per texel instead of writing 24 B and reading 24 B.  Built in this translation unit (-fmad=false),
+// so the evolution arithmetic is not FMA-contracted: it differs from ocean_rows_kernel's by rounding only
+// (both are within the stated tolerance of the oracle; tests/test_gpu_parity.py).
+// Measured on B200 (profiles/r1_f_ensemble.txt, 3 x 512^2 per instance): the spectrum is ALU-bound, its memory
+// traffic was already hidden, and the fused kernel runs the transcendental code at 24-28 warps per SM instead of
+// 48: 41.6 us per instance against 38.0 us with the separate kernels.  It therefore stays opt-in
+// (OCEAN_ENSEMBLE_FUSED_INIT=1); what it does buy is memory: 40 B per texel-cascade of pooled h0 / waveHot
+// buffers are not allocated.
+#ifndef OCEAN_RFN_MINB512
+#define OCEAN_RFN_MINB512 6  // 80 registers: measured best of 1 / 5 / 6 / 7 CTAs per SM at 3 x 512^2
+#endif
+template <int N> struct RowsFromNoiseCfg {
+    static constexpr int T = N / 8;
+    static constexpr int THREADS = 2 * T;
+    static constexpr int MINB = N == 512 ? OCEAN_RFN_MINB512 : 1;
+    using FFT = LineFFT<N, 2, false, false, false>;
+    // exchange buffer (2 rows) + h0(k) of both rows + (1/|k|, omega) of both rows
+    static constexpr int SMEM_BYTES = FFT::SMEM_BYTES + 2 * N * 8 + 2 * N * 8;
+};
+
+template <int N>
+__global__ void __launch_bounds__(RowsFromNoiseCfg<N>::THREADS, RowsFromNoiseCfg<N>::MINB) ocean_rows_from_noise_kernel(const InitArgs ia, const FrameArgs a) {
+    using Cfg = RowsFromNoiseCfg<N>;
+    using FFT = typename Cfg::FFT;
+    constexpr int T = Cfg::T;
+    extern __shared__ float4 smem[];
+    float4* xb = smem;                             // [2][N] exchange buffer
+    float2* H = (float2*)(smem + 2 * N);           // [2][N] h0(k)
+    float2* Wv = H + 2 * N;                        // [2][N] (1/|k|, omega)
+    const int t = threadIdx.x;
+    const int layer = blockIdx.x / (N / 2), pr = blockIdx.x - layer * (N / 2);
+    const bool selfPair = pr == 0;                 // rows 0 and N/2: IS:139 maps each onto itself
+    const int yA = selfPair ? 0 : pr, yB = selfPair ? N / 2 : N - pr;
+    const int st = layer / ia.C, ci = layer - st * ia.C;
+    const StateConsts sc = ia.states[st];
+    const CascadeConsts cc = ia.casc[ci];
+    const float2* __restrict__ noise = ia.noise + (size_t)st * N * N;
+
+    // ---- IS:99-143 for the two rows -> shared memory ------------------------------------------
+    if (!selfPair) {
+        // all 2T threads share row yA (4 texels each); a texel's mirror lies in row yB
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+            const int x = t + 2 * T * jj;
+            const int mx = (N - x) & (N - 1);
+            const float kx = (float)(x - N / 2) * cc.dk, kz = (float)(yA - N / 2) * cc.dk;      // IS:101-103, IS:111
+            const float kxm = (float)(mx - N / 2) * cc.dk, kzm = (float)(yB - N / 2) * cc.dk;
+            const Radial rd = initial_spectrum_radial(kx, kz, sc, cc, ia.sc);
+            const Texel tp = initial_spectrum_texel(kx, kz, rd, sc, cc, __ldg(&noise[(size_t)yA * N + x]));
+            const Texel tm = initial_spectrum_texel(kxm, kzm, rd, sc, cc, __ldg(&noise[(size_t)yB * N + mx]));
+            H[x] = tp.h;
+            H[N + mx] = tm.h;
+            Wv[x] = make_float2(tp.wave.y, tp.wave.w);
+            Wv[N + mx] = make_float2(tm.wave.y, tm.wave.w);
+        }
+    } else {
+        // the mirror of (x, y) is (N - x, y): a thread owns the texels {x, N - x} of its row for x <= N/2
+        const int r = t / T, tid = t - r * T, y = r ? N / 2 : 0;
+        for (int x = tid; x <= N / 2; x += T) {
+            const int mx = (N - x) & (N - 1);
+            const float kx = (float)(x - N / 2) * cc.dk, kz = (float)(y - N / 2) * cc.dk;
+            const float kxm = (float)(mx - N / 2) * cc.dk;
+            const Radial rd = initial_spectrum_radial(kx, kz, sc, cc, ia.sc);
+            const Texel tp = initial_spectrum_texel(kx, kz, rd, sc, cc, __ldg(&noise[(size_t)y * N + x]));
+            H[r * N + x] = tp.h;
+            Wv[r * N + x] = make_float2(tp.wave.y, tp.wave.w);
+            if (mx != x) {
+                const Texel tm = initial_spectrum_texel(kxm, kz, rd, sc, cc, __ldg(&noise[(size_t)y * N + mx]));
+                H[r * N + mx] = tm.h;
+                Wv[r * N + mx] = make_float2(tm.wave.y, tm.wave.w);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- TD:20-47 + the x-direction inverse FFT (FFT:48-57) of this thread's row -----------------
+    const int r = t / T, tid = t - r * T;
+    const int y = r ? yB : yA;
+    const int mr = selfPair ? r : 1 - r;           // the row that holds this row's mirrored texels
+    const float dk = a.dk[layer % a.C];
+    const float kz = (float)(y - N / 2) * dk;
+    C2 pa[8], pb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int x = tid + T * j;
+        const int mx = (N - x) & (N - 1);
+        const float2 h = H[r * N + x], hm = H[mr * N + mx];
+        const float kx = (float)(x - N / 2) * dk;
+        evolve_texel(make_float4(h.x, h.y, hm.x, -hm.y), Wv[r * N + x], kx, kz, a.time, pa[j], pb[j]);  // IS:141 packing
+    }
+    FFT::run(pa, xb, tid, r, a.twiddle, 0);
+    if (t == 0) spin_until_ge(a.colsDone + layer, a.colsTarget);  // write-after-read on the workspace (see ocean_rows_kernel)
+    __syncthreads();
+    {
+        float4* __restrict__ out = a.rowsA + ((size_t)layer * N + y) * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pa[j]);
+    }
+    FFT::run(pb, xb, tid, r, a.twiddle, FFT::EXCHANGES);
+    {
+        float4* __restrict__ out = a.rowsB + ((size_t)layer * N + y) * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c2_store(&out[tid + T * j], pb[j]);
+    }
+    __syncthreads();
+    if (t == 0) {
+        __threadfence();
+        atomicAdd(a.rowsDone + layer, 2ull);
+    }
+}
+
+bool rows_from_noise_available(int N) { return N == 128 || N == 256 || N == 512 || N == 1024 || N == 2048; }
+
+template <int N> static cudaError_t rows_from_noise_launch(const InitArgs& ia, const FrameArgs& a, cudaStream_t s) {
+    using Cfg = RowsFromNoiseCfg<N>;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(ocean_rows_from_noise_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        cudaFuncSetAttribute(ocean_rows_from_noise_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured = true;
+    }
+    ocean_rows_from_noise_kernel<N><<<(unsigned)(a.layers * (N / 2)), Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(ia, a);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaStream_t s) {
+    switch (a.N) {
+        case 128: return rows_from_noise_launch<128>(ia, a, s);
+        case 256: return rows_from_noise_launch<256>(ia, a, s);
+        case 512: return rows_from_noise_launch<512>(ia, a, s);
+        case 1024: return rows_from_noise_launch<1024>(ia, a, s);
+        case 2048: return rows_from_noise_launch<2048>(ia, a, s);
+        default: return cudaErrorNotSupported;
     }
 }
 

@@ -112,6 +112,11 @@ cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4*
 // launchers (return cudaGetLastError()); every launch bumps the launch counter
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
 cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
+// Initial spectrum fused into the row pass: noise -> h0 (shared memory only) -> evolution -> x-FFT
+// -> workspace planes, for oceans that are evolved once from a fresh spectrum.  InitArgs::h0 / wave / waveHot are
+// not written.  The static `configured` flag is per process and per size: call with the target device current.
+bool rows_from_noise_available(int N);
+cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaStream_t s);
 // early: the row pass may start before the previous kernel in the stream has finished (PDL).  Only
 // legal when that kernel does not produce h0 / waveHot / twiddles (i.e. it is a column pass).
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early);

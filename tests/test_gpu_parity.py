@@ -381,13 +381,37 @@ def test_reinit_after_parameter_change(pkg, po):
     body.OnDisable()
 
 
+def _ensemble_env(value):
+    """OCEAN_ENSEMBLE_FUSED_INIT is read when an ensemble is created."""
+    import contextlib, os
+
+    @contextlib.contextmanager
+    def cm():
+        old = os.environ.get("OCEAN_ENSEMBLE_FUSED_INIT")
+        if value is None:
+            os.environ.pop("OCEAN_ENSEMBLE_FUSED_INIT", None)
+        else:
+            os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = value
+        try:
+            yield
+        finally:
+            if old is None:
+                os.environ.pop("OCEAN_ENSEMBLE_FUSED_INIT", None)
+            else:
+                os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = old
+    return cm()
+
+
 def test_ensemble_equals_individual_runs(pkg, po):
-    """Ensemble runner (config 5 shape, reduced): every state == a stand-alone WaterBody with the same
-    parameters and seed, bit for bit; checksums match the arrays; waves of `batch` cover ragged counts."""
+    """Ensemble runner (default: separate spectrum kernel; config 5 shape, reduced): every state == a stand-alone
+    WaterBody with the same parameters and seed, bit for bit; checksums match the arrays; waves of `batch` cover
+    ragged counts."""
     cfg = pkg.scene.config(5)
     N = 128
     oceans, seeds = pkg.scene.ensemble_states(7)
-    ens = pkg.OceanEnsemble(N, cfg["cascades"], batch=3)
+    with _ensemble_env(None):
+        ens = pkg.OceanEnsemble(N, cfg["cascades"], batch=3)
+        again = pkg.OceanEnsemble(N, cfg["cascades"], batch=4)
     sums = ens.run(oceans, seeds, time=1.0)
     assert sums.shape == (7, 3)
     last = ens.copy_output(pkg._lib.DISPLACEMENT, 0)  # last wave held state 6 in slot 0
@@ -407,10 +431,48 @@ def test_ensemble_equals_individual_runs(pkg, po):
     ob = po.OracleB(N, tuple(float(v) for v in o), cfg["cascades"], po.fill_noise(int(seeds[3]), N))
     ob.init_spectrum()
     ob.step(1.0)
-    again = pkg.OceanEnsemble(N, cfg["cascades"], batch=4)
     again.run(oceans[:4], seeds[:4], time=1.0)
     check_fields(again.copy_output(pkg._lib.DISPLACEMENT, 3), ob.get(po.DISP), "ensemble displacement")
     assert sums[:4].tolist() == again.run(oceans[:4], seeds[:4], time=1.0).tolist()
+    ens.close()
+    again.close()
+
+
+@pytest.mark.parametrize("N", [128, 256, 512])
+def test_ensemble_with_the_spectrum_fused_into_the_row_pass(pkg, po, N):
+    """Opt-in ensemble path (ocean_rows_from_noise_kernel; OCEAN_ENSEMBLE_FUSED_INIT=1): h0 never reaches memory.  Every state
+    is within the field tolerance of the oracle (all three arrays) and of a stand-alone WaterBody, the checksums
+    are those of the arrays the ensemble holds, do not depend on the pool size, and the self-mirrored rows
+    (0 and N/2) and ragged last waves are covered."""
+    cfg = pkg.scene.config(5)
+    n = 5 if N < 512 else 3
+    oceans, seeds = pkg.scene.ensemble_states(n)
+    with _ensemble_env("1"):
+        ens = pkg.OceanEnsemble(N, cfg["cascades"], batch=2)
+        again = pkg.OceanEnsemble(N, cfg["cascades"], batch=n)
+    sums = ens.run(oceans, seeds, time=1.0)
+    assert sums.tolist() == again.run(oceans, seeds, time=1.0).tolist()
+    assert sums.tolist() == ens.run(oceans, seeds, time=1.0).tolist()
+    ids = (pkg._lib.DISPLACEMENT, pkg._lib.DERIVATIVES, pkg._lib.TURBULENCE)
+    for i in range(n):
+        got = [again.copy_output(w, i) for w in ids]
+        for k in range(3):
+            assert int(got[k].view(np.uint32).astype(np.uint64).sum()) == int(sums[i, k])
+        if i in (0, n - 1):
+            o = oceans[i]
+            ob = po.OracleB(N, tuple(float(v) for v in o), cfg["cascades"], po.fill_noise(int(seeds[i]), N), threads=8)
+            ob.init_spectrum()
+            ob.step(1.0)
+            check_fields(got[0], ob.get(po.DISP), "fused-init ensemble displacement")
+            check_fields(got[1], ob.get(po.DERIV), "fused-init ensemble derivatives")
+            check_turbulence(got[2], ob.get(po.TURB))
+            body = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5],
+                                 texturesSize=N, cascades=cfg["cascades"], seed=int(seeds[i])).Awake()
+            body.CalculateWavesTexturesAtTime(1.0)
+            check_fields(got[0], body.displacementsTextures, "fused-init ensemble vs stand-alone ocean")
+            body.OnDisable()
+    # the last wave of `ens` was ragged (n odd, batch 2): slot 0 holds the last state
+    assert np.array_equal(ens.copy_output(ids[0], 0), again.copy_output(ids[0], n - 1))
     ens.close()
     again.close()
 
