@@ -7,9 +7,20 @@ import oceanpkg
 HERE = os.path.dirname(os.path.abspath(__file__))
 VARIANTS = {
     "base": [],
+    # sensitivity builds (OCEAN_EXP bits, ocean_frame.cu): results are wrong on purpose, only the timing matters
+    "x01_rows_l2_loads": ["-DOCEAN_EXP=1"],
+    "x02_cols_no_store": ["-DOCEAN_EXP=2"],
     "x04_no_turb_load": ["-DOCEAN_EXP=4"],
-    "x16_2cta": ["-DOCEAN_EXP=16", "-DOCEAN_COLS_TMA_CTAS_PER_SM=2"],
-    "x16_3cta": ["-DOCEAN_EXP=16", "-DOCEAN_COLS_TMA_CTAS_PER_SM=3"],
+    "x08_rows_no_store": ["-DOCEAN_EXP=8"],
+    "x15_no_hbm": ["-DOCEAN_EXP=15"],
+    "x32_no_sincos": ["-DOCEAN_EXP=32"],
+    "x47_no_hbm_no_sincos": ["-DOCEAN_EXP=47"],
+    "x64_counters_only": ["-DOCEAN_EXP=64"],
+    "x128_return": ["-DOCEAN_EXP=128"],
+    # alternatives of the same arithmetic
+    "fast_sincos": ["-DOCEAN_ROWS_FAST_SINCOS=1"],
+    "early_producer": ["-DOCEAN_COLS_EARLY_PRODUCER=1"],
+    "rows_r2": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
@@ -20,7 +31,7 @@ if __name__ == "__main__":
         cmd = ["nvcc", "-ccbin", "g++"] + bm.ARCH + [f for f in bm.COMMON if f not in ("-Xptxas", "-v")] + VARIANTS[n] + ["-c", os.path.join(bm.CSRC, "ocean_frame.cu"), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode: print(n, "FAILED", r.stderr[-2000:]); continue
-        info = re.findall(r"ocean_(rows|rows_seq|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
+        info = re.findall(r"ocean_(rows|cols|cols_tma)_kernelILi512E.*?\n.*?(\d+) bytes spill stores.*?\n.*?Used (\d+) registers", r.stderr)
         others = [os.path.join(bm.OBJ, o) for o in ("ocean_init.o", "ocean_host.o", "ocean_surface.o")]
         subprocess.check_call(["nvcc", "-ccbin", "g++"] + bm.ARCH + ["-shared", "-o", os.path.join(HERE, "lib_%s.so" % n), obj] + others)
         os.remove(obj)
