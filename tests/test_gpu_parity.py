@@ -381,25 +381,43 @@ def test_reinit_after_parameter_change(pkg, po):
     body.OnDisable()
 
 
-def _ensemble_env(value):
-    """OCEAN_ENSEMBLE_FUSED_INIT is read when an ensemble is created."""
+def _ensemble_env(value, name="OCEAN_ENSEMBLE_FUSED_INIT"):
+    """OCEAN_ENSEMBLE_FUSED_INIT / OCEAN_ENSEMBLE_LANES are read when an ensemble is created."""
     import contextlib, os
 
     @contextlib.contextmanager
     def cm():
-        old = os.environ.get("OCEAN_ENSEMBLE_FUSED_INIT")
+        old = os.environ.get(name)
         if value is None:
-            os.environ.pop("OCEAN_ENSEMBLE_FUSED_INIT", None)
+            os.environ.pop(name, None)
         else:
-            os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = value
+            os.environ[name] = value
         try:
             yield
         finally:
             if old is None:
-                os.environ.pop("OCEAN_ENSEMBLE_FUSED_INIT", None)
+                os.environ.pop(name, None)
             else:
-                os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = old
+                os.environ[name] = old
     return cm()
+
+
+def test_ensemble_lanes_do_not_change_results(pkg, po):
+    """Waves alternate between two lanes (streams + pooled buffers) by default; one lane gives the same checksums,
+    and so does a second run on the same runner (every wave restarts its lane's counters and buffers)."""
+    cfg = pkg.scene.config(5)
+    oceans, seeds = pkg.scene.ensemble_states(9)
+    with _ensemble_env("1", "OCEAN_ENSEMBLE_LANES"):
+        one = pkg.OceanEnsemble(256, cfg["cascades"], batch=2)
+    with _ensemble_env(None, "OCEAN_ENSEMBLE_LANES"):
+        two = pkg.OceanEnsemble(256, cfg["cascades"], batch=2)
+    want = one.run(oceans, seeds, time=0.5)
+    assert want.tolist() == two.run(oceans, seeds, time=0.5).tolist()
+    assert want.tolist() == two.run(oceans, seeds, time=0.5).tolist()
+    # 9 states in waves of 2: the last (ragged) wave ran on lane 0; its slot 0 holds state 8
+    assert np.array_equal(one.copy_output(pkg._lib.TURBULENCE, 0), two.copy_output(pkg._lib.TURBULENCE, 0))
+    one.close()
+    two.close()
 
 
 def test_ensemble_equals_individual_runs(pkg, po):
