@@ -456,7 +456,25 @@ def test_ensemble_equals_individual_runs(pkg, po):
     again.close()
 
 
-@pytest.mark.parametrize("N", [128, 256, 512])
+def test_fused_spectrum_request_falls_back_below_128(pkg, po):
+    """ocean_rows_from_noise_kernel covers N >= 128; smaller ensembles ignore OCEAN_ENSEMBLE_FUSED_INIT and stay bit-identical
+    to stand-alone oceans."""
+    cfg = pkg.scene.config(5)
+    oceans, seeds = pkg.scene.ensemble_states(3)
+    with _ensemble_env("1"):
+        ens = pkg.OceanEnsemble(64, cfg["cascades"], batch=2)
+    sums = ens.run(oceans, seeds, time=1.0)
+    o = oceans[2]
+    body = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5],
+                         texturesSize=64, cascades=cfg["cascades"], seed=int(seeds[2])).Awake()
+    body.CalculateWavesTexturesAtTime(1.0)
+    assert np.array_equal(ens.copy_output(pkg._lib.DISPLACEMENT, 0), body.displacementsTextures)
+    assert int(body.derivativesTextures.view(np.uint32).astype(np.uint64).sum()) == int(sums[2, 1])
+    body.OnDisable()
+    ens.close()
+
+
+@pytest.mark.parametrize("N", [128, 256, 512, 1024])
 def test_ensemble_with_the_spectrum_fused_into_the_row_pass(pkg, po, N):
     """Opt-in ensemble path (ocean_rows_from_noise_kernel; OCEAN_ENSEMBLE_FUSED_INIT=1): h0 never reaches memory.  Every state
     is within the field tolerance of the oracle (all three arrays) and of a stand-alone WaterBody, the checksums
