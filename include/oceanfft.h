@@ -184,6 +184,25 @@ int ocean_copy_mip(OceanHandle* h, int which, int level, int cascade, float* hos
 int ocean_sample_surface(OceanHandle* h, const float* worldXZ, int n, float lod, float* displacement, float* normal,
                          float* foam, int onDevice);
 
+/* ---- buoyancy: BuoyantObject.FixedUpdate BO:18-30 for a batch of boxes ----------- */
+
+/* transform.position and transform.localScale of one BuoyantObject */
+typedef struct OceanBuoyantBox {
+    float px, py, pz;
+    float sx, sy, sz;
+} OceanBuoyantBox;
+
+/* For each of the n boxes, in the reference's fp32 operation order:
+ *   waterHeight     = GetWaterHeight(position)            BO:18  (any OceanQueryMode but READBACK_REF; NEAREST_REF is
+ *                                                                 the reference's lookup on the current frame)
+ *   heightSubmerged = max(0, waterHeight - py)             BO:19
+ *   submergedVolume = clamp(heightSubmerged / sy, 0, 1) * (sx * sy * sz)      BO:24-25 (0 when not submerged, BO:21)
+ *   acceleration    = |gravityY| * (density * submergedVolume)                 BO:26-29, the upward ForceMode.Acceleration
+ * out4[i] = (waterHeight, heightSubmerged, acceleration, submergedVolume).  The drag terms BO:31-33 need the rigid body's
+ * velocities and stay with the caller (apply them when heightSubmerged > 0).  density = WaterBody.density (WB:18). */
+int ocean_buoyancy(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode /*OceanQueryMode*/, float density,
+                   float gravityY, float* out4, int boxesOnDevice, int outOnDevice);
+
 /* ---- foam state: the persistence implicit in the turbulence RenderTexture RF:28,32 --------- */
 int ocean_set_turbulence(OceanHandle* h, const float* host /* C*N*N*4 */);
 int ocean_reset_foam(OceanHandle* h);

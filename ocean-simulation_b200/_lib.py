@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "ocean_ensemble_create", "ocean_ensemble_destroy", "ocean_ensemble_run",
     "ocean_ensemble_get_output", "ocean_ensemble_copy_output",
     "ocean_generate_mips", "ocean_set_auto_mips", "ocean_mip_levels", "ocean_get_mips", "ocean_copy_mip",
-    "ocean_sample_surface",
+    "ocean_sample_surface", "ocean_buoyancy",
 ]
 
 
@@ -41,6 +41,11 @@ class OceanParams(ctypes.Structure):
 class OceanCascade(ctypes.Structure):
     _fields_ = [("wavelength", ctypes.c_float), ("cutoffLow", ctypes.c_float), ("cutoffHigh", ctypes.c_float),
                 ("swell", ctypes.c_float), ("fade", ctypes.c_float)]
+
+
+class OceanBuoyantBox(ctypes.Structure):
+    _fields_ = [("px", ctypes.c_float), ("py", ctypes.c_float), ("pz", ctypes.c_float),
+                ("sx", ctypes.c_float), ("sy", ctypes.c_float), ("sz", ctypes.c_float)]
 
 
 class OceanError(RuntimeError):
@@ -106,6 +111,7 @@ def load():
     L.ocean_get_mips.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     L.ocean_copy_mip.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, fp]
     L.ocean_sample_surface.argtypes = [vp, vp, ctypes.c_int, ctypes.c_float, vp, vp, vp, ctypes.c_int]
+    L.ocean_buoyancy.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp, ctypes.c_int, ctypes.c_int]
     _lib = L
     return L
 

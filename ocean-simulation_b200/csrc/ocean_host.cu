@@ -327,6 +327,8 @@ struct OceanHandle {
     unsigned long long auxSignals = 0;      // its value once every reader launched so far has finished
     // surface-sample scratch: n x (2 in + 7 out) floats
     float* sBuf = nullptr;
+    float4* bBuf = nullptr;  // ocean_buoyancy scratch: out4 | points | heights | boxes, bCap boxes
+    int bCap = 0;
     int sCap = 0;
 
     size_t texels() const { return (size_t)N * N; }
@@ -340,6 +342,7 @@ struct OceanHandle {
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
     int AttachWorkspace(cudaStream_t shared);
     int GenerateMips();
+    int Buoyancy(const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4, bool boxesDev, bool outDev);
     int SampleSurface(const float* worldXZ, int n, float lod, float* disp3, float* normal3, float* foam, bool onDevice);
     void OnDisable();
 };
@@ -463,6 +466,42 @@ int OceanHandle::GenerateMips() {
     // next column pass spinning for them, back-to-back frames starved the chain kernels of SM resources and
     // deadlocked; ordering that pass after them with an event instead cost 43.0 us per frame + chains
     // against 38.7 us for this in-stream programmatic chain.)
+    return OCEAN_OK;
+}
+
+// BuoyantObject.FixedUpdate BO:18-30 for n boxes: gather the query points, any device query mode, the force epilogue.
+int OceanHandle::Buoyancy(const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4, bool boxesDev,
+                          bool outDev) {
+    if (n == 0) return OCEAN_OK;
+    if (n > bCap) {
+        if (bBuf) cudaFree(bBuf);
+        bBuf = nullptr; bCap = 0;
+        OCEAN_CUDA(cudaMalloc(&bBuf, (size_t)n * (sizeof(float4) + sizeof(float2) + sizeof(float) + sizeof(OceanBuoyantBox))));
+        bCap = n;
+    }
+    float4* dOut = bBuf;
+    float2* dPts = (float2*)(dOut + n);
+    float* dHeights = (float*)(dPts + n);
+    OceanBuoyantBox* dBoxes = (OceanBuoyantBox*)(dHeights + n);
+    const OceanBuoyantBox* bx = boxes;
+    if (!boxesDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(dBoxes, boxes, (size_t)n * sizeof(OceanBuoyantBox), cudaMemcpyHostToDevice, stream));
+        bx = dBoxes;
+    }
+    OCEAN_CUDA(launch_buoyancy_points(bx, dPts, n, stream));
+    float wl[OCEAN_MAX_CASCADES];
+    for (int i = 0; i < C; ++i) wl[i] = cascades[i].wavelength;
+    if (mode == OCEAN_QUERY_DISPLACED) {
+        OCEAN_CUDA(launch_displaced_query(disp, N, C, wl, dPts, dHeights, n, OCEAN_DISPLACED_ITERATIONS, stream));
+    } else {
+        OCEAN_CUDA(launch_query(disp, N, C, wl, dPts, dHeights, n, mode, stream));
+    }
+    float4* out = outDev ? (float4*)out4 : dOut;
+    OCEAN_CUDA(launch_buoyancy(bx, dHeights, n, density, gravityY, out, stream));
+    if (!outDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(out4, dOut, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, stream));
+        OCEAN_CUDA(cudaStreamSynchronize(stream));
+    }
     return OCEAN_OK;
 }
 
@@ -636,7 +675,7 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, auxDone};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, bBuf, auxDone};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -1017,6 +1056,17 @@ int ocean_query_heights(OceanHandle* h, const float* worldXZ, int n, int mode, f
     if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_DISPLACED) return fail(OCEAN_ERR_INVALID_ARGUMENT, "unknown query mode %d", mode);
     DeviceScope scope(h->device);
     return h->GetWaterHeight(worldXZ, n, mode, heights, pointsOnDevice != 0, heightsOnDevice != 0);
+}
+
+int ocean_buoyancy(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4,
+                   int boxesOnDevice, int outOnDevice) {
+    if (!h || (n > 0 && (!boxes || !out4))) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
+    if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_DISPLACED || mode == OCEAN_QUERY_READBACK_REF)
+        return fail(OCEAN_ERR_INVALID_ARGUMENT, "ocean_buoyancy takes a device query mode (not %d; READBACK_REF is a host lookup)", mode);
+    if (!h->spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_buoyancy before ocean_init_spectrum");
+    DeviceScope scope(h->device);
+    return h->Buoyancy(boxes, n, mode, density, gravityY, out4, boxesOnDevice != 0, outOnDevice != 0);
 }
 
 int ocean_generate_mips(OceanHandle* h) {

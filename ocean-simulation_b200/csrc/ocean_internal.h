@@ -141,6 +141,10 @@ cudaError_t launch_surface(const float4* disp, const float4* deriv, const float4
                            float* outNormal, float* outFoam, cudaStream_t s);
 cudaError_t launch_displaced_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                                    float* out, int n, int iterations, cudaStream_t s);
+// BuoyantObject.FixedUpdate BO:18-30: boxes -> query points (gather), heights -> (height, submerged, acceleration, volume)
+cudaError_t launch_buoyancy_points(const OceanBuoyantBox* boxes, float2* pts, int n, cudaStream_t s);
+cudaError_t launch_buoyancy(const OceanBuoyantBox* boxes, const float* heights, int n, float density, float gravityY, float4* out,
+                            cudaStream_t s);
 cudaError_t launch_pack_height(const float4* dispLayer, float* out, int n, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
                             int outStride, cudaStream_t s);

@@ -256,6 +256,39 @@ cudaError_t launch_mip_chains(const float4* baseA, float4* mipsA, const float4* 
     return cudaGetLastError();
 }
 
+// BuoyantObject.FixedUpdate BO:18-30 for a batch of boxes (the height comes from any of the query kernels)
+__global__ void ocean_buoyancy_points_kernel(const OceanBuoyantBox* __restrict__ boxes, float2* __restrict__ pts, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) pts[i] = make_float2(boxes[i].px, boxes[i].pz);  // GetWaterHeight reads worldPosition.x / .z  WB:199-200
+}
+__global__ void ocean_buoyancy_kernel(const OceanBuoyantBox* __restrict__ boxes, const float* __restrict__ heights, int n,
+                                      float density, float absGravityY, float4* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const OceanBuoyantBox b = boxes[i];
+    const float waterHeight = heights[i];                                  // BO:18
+    const float heightSubmerged = fmaxf(0.0f, waterHeight - b.py);        // BO:19
+    float volume = 0.0f, accel = 0.0f;
+    if (heightSubmerged > 0.0f) {                                          // BO:21
+        const float fullVolume = b.sx * b.sy * b.sz;                       // BO:24
+        volume = fminf(fmaxf(heightSubmerged / b.sy, 0.0f), 1.0f) * fullVolume;  // BO:25
+        const float buoyantForce = density * volume;                       // BO:26
+        accel = absGravityY * buoyantForce;                                // BO:29
+    }
+    out[i] = make_float4(waterHeight, heightSubmerged, accel, volume);
+}
+cudaError_t launch_buoyancy_points(const OceanBuoyantBox* boxes, float2* pts, int n, cudaStream_t s) {
+    ocean_buoyancy_points_kernel<<<(n + 255) / 256, 256, 0, s>>>(boxes, pts, n);
+    count_launch();
+    return cudaGetLastError();
+}
+cudaError_t launch_buoyancy(const OceanBuoyantBox* boxes, const float* heights, int n, float density, float gravityY, float4* out,
+                            cudaStream_t s) {
+    ocean_buoyancy_kernel<<<(n + 255) / 256, 256, 0, s>>>(boxes, heights, n, density, fabsf(gravityY), out);
+    count_launch();
+    return cudaGetLastError();
+}
+
 static void fill_wavelengths(float* dst, const float* wavelengths, int C) {
     for (int i = 0; i < OCEAN_MAX_CASCADES; ++i) dst[i] = i < C ? wavelengths[i] : 1.0f;
 }

@@ -186,6 +186,15 @@ class WaterBody:
         L.check(self._lib.ocean_sample_surface(self._need(), pts.ctypes.data, n, float(lod), ptr(d), ptr(nr), ptr(f), 0))
         return d, nr, f
 
+    def Buoyancy(self, boxes, mode=L.QUERY_NEAREST_REF, density=1.0, gravityY=-9.81):
+        """BuoyantObject.FixedUpdate BO:18-30 for a batch: boxes [n][6] = (position xyz, localScale xyz) ->
+        [n][4] = (waterHeight, heightSubmerged, upward acceleration, submergedVolume).  density = WaterBody.density WB:18."""
+        b = np.ascontiguousarray(boxes, np.float32).reshape(-1, 6)
+        out = np.empty((b.shape[0], 4), np.float32)
+        L.check(self._lib.ocean_buoyancy(self._need(), b.ctypes.data, b.shape[0], int(mode), float(density), float(gravityY),
+                                         out.ctypes.data, 0, 0))
+        return out
+
     def SetReadbackMode(self, mode):
         """L.READBACK_RGBA (the reference's whole-layer request, default) or L.READBACK_HEIGHT (packed .g only)."""
         L.check(self._lib.ocean_set_readback_mode(self._need(), int(mode)))

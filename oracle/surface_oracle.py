@@ -107,3 +107,22 @@ def displaced_heights(disp, wavelengths, world_xz, iterations=4, return_q=False)
         lastq = (qx, qz)
         qx, qz = (p[:, 0] - d[:, 0]).astype(F), (p[:, 1] - d[:, 2]).astype(F)
     return (height, lastq) if return_q else height
+
+
+def buoyancy(water_height, boxes, density=1.0, gravity_y=-9.81):
+    """BuoyantObject.FixedUpdate BO:18-30 in fp32, operation for operation: water_height [n] (WaterBody.GetWaterHeight at each
+    box position, BO:18), boxes [n][6] = (transform.position xyz, transform.localScale xyz) ->
+    [n][4] = (waterHeight, heightSubmerged, upward acceleration |g.y| * density * submergedVolume, submergedVolume)."""
+    f = np.float32
+    wh = np.asarray(water_height, f)
+    b = np.asarray(boxes, f).reshape(-1, 6)
+    py, sx, sy, sz = b[:, 1], b[:, 3], b[:, 4], b[:, 5]
+    sub = np.maximum(f(0), wh - py)                                     # BO:19
+    with np.errstate(divide="ignore", invalid="ignore"):
+        full = (sx * sy) * sz                                           # BO:24
+        vol = np.clip(sub / sy, f(0), f(1)) * full                      # BO:25
+        acc = f(abs(gravity_y)) * (f(density) * vol)                    # BO:26, BO:29
+    wet = sub > 0                                                       # BO:21
+    vol = np.where(wet, vol, f(0)).astype(f)
+    acc = np.where(wet, acc, f(0)).astype(f)
+    return np.stack([wh, sub.astype(f), acc, vol], axis=1)

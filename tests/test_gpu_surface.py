@@ -216,3 +216,43 @@ def test_surface_full_size_properties(pkg, po):
     assert np.allclose(np.linalg.norm(n.astype(np.float64), axis=1), 1.0, atol=1e-6)
     assert (n[:, 1] > 0).all() and f.min() >= 0 and f.max() <= 4
     body.OnDisable()
+
+
+@pytest.mark.parametrize("mode_name", ["QUERY_NEAREST_REF", "QUERY_BILINEAR_ALL_CASCADES", "QUERY_DISPLACED"])
+def test_buoyancy_matches_the_oracle_bit_for_bit(pkg, po, so, mode_name):
+    """ocean_buoyancy = BuoyantObject.FixedUpdate BO:18-30 for a batch of boxes: the height is the query kernel's, the force
+    epilogue is compared bit for bit with the fp32 oracle fed with those heights; boxes above, across and below the surface."""
+    L = pkg._lib
+    mode = getattr(L, mode_name)
+    cfg, body, _ = stepped_body(pkg, po)
+    N = body.texturesSize
+    rng = np.random.default_rng(11)
+    n = 4099
+    boxes = np.empty((n, 6), np.float32)
+    boxes[:, 0] = rng.uniform(-N, N, n)
+    boxes[:, 2] = rng.uniform(-N, N, n)
+    boxes[:, 1] = rng.uniform(-3.0, 3.0, n)          # around the surface
+    boxes[:, 3:6] = rng.uniform(0.2, 4.0, (n, 3))
+    boxes[0, 1], boxes[1, 1] = 1e4, -1e4             # far above, far below
+    heights = body.GetWaterHeights(boxes[:, [0, 2]], mode)
+    got = body.Buoyancy(boxes, mode, density=1.0, gravityY=-9.81)
+    want = so.buoyancy(heights, boxes, density=1.0, gravity_y=-9.81)
+    assert np.array_equal(got, want)
+    assert got[0, 1] == 0 and got[0, 2] == 0 and got[0, 3] == 0
+    assert got[1, 3] == np.float32(np.float32(boxes[1, 3] * boxes[1, 4]) * boxes[1, 5])  # fully submerged: the whole volume
+    assert (got[:, 1] > 0).sum() > n // 4 and (got[:, 1] == 0).sum() > n // 4
+    body.OnDisable()
+
+
+def test_buoyancy_argument_errors(pkg, po):
+    import ctypes
+    L = pkg._lib
+    lib = L.load()
+    cfg, body, _ = stepped_body(pkg, po, N=64, frames=1)
+    box = np.zeros((1, 6), np.float32)
+    out = np.zeros((1, 4), np.float32)
+    assert lib.ocean_buoyancy(body._h, box.ctypes.data, 1, L.QUERY_READBACK_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_buoyancy(body._h, None, 1, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_buoyancy(body._h, box.ctypes.data, -1, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.ERR_INVALID_ARGUMENT
+    assert lib.ocean_buoyancy(body._h, box.ctypes.data, 0, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.OK
+    body.OnDisable()

@@ -111,3 +111,15 @@ def test_displaced_heights_invert_a_gerstner_wave():
     assert np.abs(h0 - A * np.cos(k * q)).max() > 0.3
     h4 = so.displaced_heights(disp, [wl], X, iterations=4)
     assert np.abs(h4 - A * np.cos(k * q)).max() < A * (A * k) ** 5 * 3 + 2e-3
+
+
+def test_buoyancy_oracle_closed_forms():
+    """BO:18-30: a 1 x 2 x 3 box whose centre is 0.5 below the water line is a quarter submerged (0.5 / sy), one far below is
+    fully submerged (clamp), one above the water feels nothing."""
+    from oracle import surface_oracle as so
+    boxes = np.array([[0, -0.5, 0, 1, 2, 3], [5, -10.0, 5, 1, 2, 3], [0, 4.0, 0, 1, 2, 3]], np.float32)
+    out = so.buoyancy(np.array([0.0, 1.0, 3.5], np.float32), boxes, density=2.0, gravity_y=-10.0)
+    assert np.allclose(out[0], [0.0, 0.5, 10.0 * 2.0 * 0.25 * 6.0, 0.25 * 6.0])
+    assert np.allclose(out[1], [1.0, 11.0, 10.0 * 2.0 * 6.0, 6.0])
+    assert np.array_equal(out[2], np.array([3.5, 0.0, 0.0, 0.0], np.float32))
+    assert out.dtype == np.float32
