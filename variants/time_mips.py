@@ -34,3 +34,8 @@ for lod in (0.0, 1.5):
 for mode in (L.QUERY_BILINEAR_ALL_CASCADES, L.QUERY_DISPLACED):
     t = timeit(lambda: L.check(body._lib.ocean_query_heights(body._h, P(pts), n, mode, P(h), 1, 1)), 50)
     print("query mode %d 1M points: %.1f us (%.2f Gpoints/s)" % (mode, t, n / t / 1e3))
+boxes = torch.empty(n, 6, device="cuda"); boxes[:, 0] = pts[:, 0]; boxes[:, 2] = pts[:, 1]; boxes[:, 1] = (torch.rand(n, device="cuda") - 0.5) * 4; boxes[:, 3:] = 1.0
+out4 = torch.empty(n, 4, device="cuda")
+for mode in (L.QUERY_NEAREST_REF, L.QUERY_BILINEAR_ALL_CASCADES, L.QUERY_DISPLACED):
+    t = timeit(lambda: L.check(body._lib.ocean_buoyancy(body._h, P(boxes), n, mode, 1.0, -9.81, P(out4), 1, 1)), 50)
+    print("buoyancy (BO:18-30) mode %d 1M boxes: %.1f us (%.2f Gboxes/s)" % (mode, t, n / t / 1e3))
