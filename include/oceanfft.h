@@ -117,7 +117,8 @@ void ocean_destroy(OceanHandle* h);
 
 /* Live parameter edit (the commented-out OnValidate WB:324-337).  textureSize must not change;
  * cascades may be NULL to keep the current ones, otherwise nCascades must equal the handle's.
- * Takes effect at the next ocean_init_spectrum. */
+ * The edit is staged: frames, queries and samplers keep using the parameter set the spectrum on the device
+ * was computed from (wavelengths, dk, lambda) until the next ocean_init_spectrum commits it. */
 int ocean_set_params(OceanHandle* h, const OceanParams* params, const OceanCascade* cascades, int nCascades);
 
 /* CalculateInitialSpectrumTextures WB:171-178: IS:99-129 then IS:135-143, one fused kernel. */
@@ -225,7 +226,9 @@ int ocean_describe(OceanHandle* h, char* buf, size_t bufBytes);
 /* ---- ensembles: many independent oceans (BASELINE config 5) -------------------------------- */
 
 /* A pooled runner for `batch` oceans of (N, nCascades) at a time on one device.  Every state
- * shares the cascade set; ocean parameters and the noise seed vary per state. */
+ * shares the cascade set; ocean parameters and the noise seed vary per state -- except OceanParams::lambda,
+ * which the frame kernels take as one scalar per wave of `batch` states: ocean_ensemble_run returns
+ * OCEAN_ERR_INVALID_PARAMS for a wave whose states do not share one lambda. */
 int ocean_ensemble_create(int textureSize, const OceanCascade* cascades, int nCascades, int batch,
                           int device, OceanEnsemble** out);
 void ocean_ensemble_destroy(OceanEnsemble* e);

@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
     const size_t base = (size_t)blockIdx.y * N * N + x;  // texel (x, 0) of this layer
     pdl_trigger();
     pdl_wait();  // the row pass of this frame (and through it every earlier kernel) has completed
-    if (a.auxDone) {  // readers of the previous frame's outputs (mip chain, host pack) may still be at work
+    if (a.auxDone) {  // readers of the previous frame's outputs (mip chain) may still be at work
         if (threadIdx.x == 0) spin_until_ge(a.auxDone, a.auxTarget);
         __syncthreads();
     }
@@ -681,10 +681,11 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twS[i] = __ldg(&a.twiddle[i]);
     __syncthreads();
 #endif
-    // No griddepcontrol.wait here: the producer gates every tile on its layer's row counter instead.
-    // A counter can only reach the target after row CTAs of THIS frame passed their own
-    // griddepcontrol.wait, i.e. after everything earlier in the stream (the previous column pass
-    // included) has completed, so completion stays transitive along the stream.
+    // No griddepcontrol.wait here, and none in the row kernels either: the producer gates every tile on its
+    // layer's row counter, and a row CTA of this frame only stores (and then counts) once colsDone[layer] says
+    // the previous column pass has finished with that layer.  The invariant that makes an `early` row pass
+    // legal is on the host side: every producer of h0 / waveHot / the twiddle table (ocean_init_spectrum,
+    // Awake) synchronises its stream before a frame can be enqueued, so nothing a row CTA reads is in flight.
     TRACE(1, blockIdx.x, 1);
 
     // tile -> TMA coordinates: c0 = first fp32 of the tile's columns, c1 = first row
@@ -764,7 +765,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         for (; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
             const int next = tile + gridDim.x;
             mbar_wait(&bars[2], parity);  // displacement staged in bufA
-            if (!auxIdle) {  // readers of the previous frame's outputs (mip chain, host pack) may still be at work
+            if (!auxIdle) {  // readers of the previous frame's outputs (mip chain) may still be at work
                 spin_until_ge(a.auxDone, a.auxTarget);
                 auxIdle = true;
             }

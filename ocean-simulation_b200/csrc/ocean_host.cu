@@ -148,13 +148,16 @@ static std::vector<float2> make_twiddles(int N) {
 // Workspace: the two intermediate planes between the row and the column pass ([layers][N][N] float4
 // each, contiguous).  It is scratch: nothing in it survives a frame.  Handles that were put on the
 // same caller-provided stream (ocean_set_stream) are serialised by that stream, so they share one
-// workspace per (device, stream, size) -- like FFT plans sharing a work area -- and the planes stay
-// resident in L2 however many oceans rotate through them.  A handle on its own stream owns a
+// workspace per (device, stream, N, layers) -- like FFT plans sharing a work area -- and the planes stay
+// resident in L2 however many oceans rotate through them.  The key is the geometry, not the byte size:
+// the hand-off counters are one per layer and their targets count rows of N texels, so a 512 x 1 and a
+// 256 x 4 ocean (equal bytes) must not meet on one workspace.  A handle on its own stream owns a
 // private workspace.
 struct Workspace {
     int device = 0;
     cudaStream_t stream = nullptr;  // nullptr: private
     size_t planeBytes = 0;
+    int N = 0;                      // texture size of every user (part of the sharing key)
     float4* base = nullptr;
     int refs = 0;
     // Hand-off counters live with the memory they guard.  counters[0..layers) = rows written into the
@@ -170,14 +173,15 @@ struct Workspace {
 static std::mutex g_wsMutex;
 static std::vector<Workspace*> g_workspaces;
 
-static Workspace* workspace_acquire(int device, cudaStream_t shared, size_t planeBytes, int layers) {
+static Workspace* workspace_acquire(int device, cudaStream_t shared, int N, int layers) {
     std::lock_guard<std::mutex> lock(g_wsMutex);
+    const size_t planeBytes = (size_t)layers * N * N * sizeof(float4);
     if (shared)
         for (Workspace* w : g_workspaces)
-            if (w->device == device && w->stream == shared && w->planeBytes == planeBytes) { ++w->refs; return w; }
+            if (w->device == device && w->stream == shared && w->N == N && w->layers == layers) { ++w->refs; return w; }
     Workspace* w = new Workspace;
     w->device = device; w->stream = shared; w->planeBytes = planeBytes; w->refs = 1;
-    w->layers = layers;
+    w->N = N; w->layers = layers;
     if (cudaMalloc(&w->base, 2 * planeBytes) != cudaSuccess) { delete w; return nullptr; }
     if (cudaMalloc(&w->counters, 2 * layers * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMemset(w->counters, 0, 2 * layers * sizeof(unsigned long long)) != cudaSuccess) {
@@ -278,8 +282,14 @@ using namespace ocean;
 struct OceanHandle {
     int device = 0;
     int N = 0, C = 0;
+    // `params` / `cascades` are the ACTIVE set: the one the spectrum on the device was computed from, and the
+    // one every frame, query and sampler uses (dk, wavelengths, lambda).  ocean_set_params only stages an edit
+    // (`nextParams` / `nextCascades`); CalculateInitialSpectrumTextures commits it, so a frame issued between
+    // the two still evolves a consistent (h0, omega, 1/|k|, dk) set.
     OceanParams params{};
     OceanCascade cascades[OCEAN_MAX_CASCADES]{};
+    OceanParams nextParams{};
+    OceanCascade nextCascades[OCEAN_MAX_CASCADES]{};
     cudaStream_t ownStream = nullptr, stream = nullptr, copyStream = nullptr;
     // arrays of WB:221-229 (+ noise WB:34); rowsA/rowsB replace the 4 spectra + ping-pong array
     float2* noise = nullptr;
@@ -322,7 +332,7 @@ struct OceanHandle {
     float4 *derivMips = nullptr, *turbMips = nullptr;
     int64_t mipsFrame = -1;  // frame index the chains were built from
     bool autoMips = false;   // rebuild them at the end of every frame, as the reference does
-    // readers of a frame's outputs that run beside the next frame (mip chains, host pack)
+    // readers of a frame's outputs that run beside the next frame (the mip chains)
     unsigned long long* auxDone = nullptr;  // device counter they bump when they stop reading
     unsigned long long auxSignals = 0;      // its value once every reader launched so far has finished
     // surface-sample scratch: n x (2 in + 7 out) floats
@@ -349,7 +359,7 @@ struct OceanHandle {
 
 // (Re)binds the intermediate planes: a private workspace, or the one shared by every handle on `shared`.
 int OceanHandle::AttachWorkspace(cudaStream_t shared) {
-    Workspace* w = workspace_acquire(device, shared, C * texels() * sizeof(float4), C);
+    Workspace* w = workspace_acquire(device, shared, N, C);
     if (!w) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
     workspace_release(ws);
     ws = w;
@@ -402,6 +412,8 @@ int OceanHandle::Awake(const float* noiseHost, uint64_t seed) {
 }
 
 int OceanHandle::CalculateInitialSpectrumTextures() {
+    params = nextParams;  // commit a staged ocean_set_params (no-op otherwise)
+    memcpy(cascades, nextCascades, sizeof cascades);
     const StateConsts sc = make_state_consts(params);
     OCEAN_CUDA(cudaMemcpyAsync(stateDev, &sc, sizeof sc, cudaMemcpyHostToDevice, stream));
     InitArgs a{};
@@ -747,7 +759,7 @@ int OceanEnsemble::create() {
         float4** arrs[] = {&L.disp, &L.deriv, &L.turb};
         for (float4** a : arrs) OCEAN_CUDA(cudaMalloc(a, (size_t)batch * C * t * sizeof(float4)));
         if (!fusedInit) OCEAN_CUDA(cudaMalloc(&L.h0, (size_t)batch * C * t * sizeof(float4)));
-        L.ws = workspace_acquire(device, nullptr, (size_t)batch * C * t * sizeof(float4), batch * C);
+        L.ws = workspace_acquire(device, nullptr, N, batch * C);
         if (!L.ws) return fail(OCEAN_ERR_CUDA, "cudaMalloc of the intermediate planes failed");
         if (!fusedInit) OCEAN_CUDA(cudaMalloc(&L.waveHot, (size_t)batch * C * t * sizeof(float2)));
         if (!fusedInit && rows_need_h0c()) OCEAN_CUDA(cudaMalloc(&L.h0c, (size_t)batch * C * t * sizeof(float2)));
@@ -790,6 +802,12 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
             p.textureSize = N;
             int rc = validate_params(p);
             if (rc != OCEAN_OK) return rc;
+            // the frame kernels take lambda as one scalar per launch (= per wave): refuse to apply the first
+            // state's value silently to the others
+            if (p.lambda != states[base].lambda)
+                return fail(OCEAN_ERR_INVALID_PARAMS, "state %d has lambda %g but its wave (states %d..%d) starts with %g: "
+                            "one ensemble wave shares one lambda (group states by lambda, or run them with batch = 1)",
+                            base + i, (double)p.lambda, base, base + nb - 1, (double)states[base].lambda);
             L.stateHost[i] = make_state_consts(p);
             L.seedHost[i] = seeds ? seeds[base + i] : (uint64_t)(base + i);
         }
@@ -892,8 +910,9 @@ int ocean_create(const OceanParams* params, const OceanCascade* cascades, int nC
     h->device = device;
     h->N = params->textureSize;
     h->C = nCascades;
-    h->params = *params;
+    h->params = h->nextParams = *params;
     memcpy(h->cascades, cascades, nCascades * sizeof(OceanCascade));
+    memcpy(h->nextCascades, cascades, nCascades * sizeof(OceanCascade));
     rc = h->Awake(noiseRG, seed);
     if (rc != OCEAN_OK) {
         h->OnDisable();
@@ -920,9 +939,9 @@ int ocean_set_params(OceanHandle* h, const OceanParams* params, const OceanCasca
         if (nCascades != h->C) return fail(OCEAN_ERR_INVALID_CASCADES, "cascade count cannot change after create (%d -> %d)", h->C, nCascades);
         rc = validate_cascades(cascades, nCascades);
         if (rc != OCEAN_OK) return rc;
-        memcpy(h->cascades, cascades, nCascades * sizeof(OceanCascade));
+        memcpy(h->nextCascades, cascades, nCascades * sizeof(OceanCascade));
     }
-    h->params = *params;
+    h->nextParams = *params;  // staged: takes effect at the next ocean_init_spectrum
     return OCEAN_OK;
 }
 
@@ -1044,6 +1063,12 @@ int ocean_reset_foam(OceanHandle* h) {
     OCEAN_CUDA(cudaMemsetAsync(h->turb, 0, h->C * h->layerBytes4(), h->stream));
     h->foamZero = true;
     h->frame = 0;
+    // the frame index restarts, so the readback ring (ordered by frame index) restarts with it: without this
+    // READBACK_REF / ocean_readback_ptr would keep answering from the newest pre-reset layer until the new
+    // index passed the old one, and that slot would be excluded from reuse for as long
+    OCEAN_CUDA(cudaStreamSynchronize(h->copyStream));
+    for (int i = 0; i < OceanHandle::RB; ++i) { h->rbPending[i] = false; h->rbFrame[i] = -1; }
+    h->rbLatest = -1;
     return OCEAN_OK;
 }
 

@@ -79,9 +79,10 @@ struct FrameArgs {
     // next frame may overwrite its rows of the workspace once colsDone[layer] >= colsTarget.
     unsigned long long* colsDone;      // device, one counter per layer
     unsigned long long colsTarget;     // N * (column passes issued before this frame)
-    // Readers of a frame's outputs that run beside the next frame (mip chains WB:191-192, the host pack of
-    // the readback WB:288) do not hold its row pass back: the column pass waits for auxDone >= auxTarget
-    // before its first store instead (nullptr: no such reader was ever launched on this ocean).
+    // Readers of a frame's outputs that run beside the next frame (today: the mip chains WB:191-192, which
+    // bump auxDone when their reads are over) do not hold its row pass back: the column pass waits for
+    // auxDone >= auxTarget before its first store instead (nullptr: no such reader was ever launched on this
+    // ocean).  The readback's snapshot / pack (WB:288) is ordered by the stream or by colsDone[0], not by this.
     const unsigned long long* auxDone;
     unsigned long long auxTarget;
     // Readback plane (WB:288, HEIGHT mode): when not nullptr the column pass also writes the .g channel of

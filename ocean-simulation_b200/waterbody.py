@@ -114,12 +114,17 @@ class WaterBody:
     def __exit__(self, *a):
         self.OnDisable()
 
-    def OnValidate(self):
-        """The reference's (commented-out) live parameter edit WB:324-337: push the current field
-        values and recompute the initial spectrum."""
+    def SetParams(self):
+        """Stages the current field values (ocean_set_params); they take effect at the next
+        CalculateInitialSpectrumTextures -- frames issued in between keep the active set."""
         p = self._params()
         _, arr = _cascade_array(self.cascades)
         L.check(self._lib.ocean_set_params(self._need(), ctypes.byref(p), arr, len(self.cascades)))
+
+    def OnValidate(self):
+        """The reference's (commented-out) live parameter edit WB:324-337: push the current field
+        values and recompute the initial spectrum."""
+        self.SetParams()
         self.CalculateInitialSpectrumTextures()
 
     # -- the path --------------------------------------------------------------------------
@@ -306,10 +311,11 @@ class OceanEnsemble:
         checksums of (displacement, derivatives, turbulence)."""
         oceans = np.asarray(oceans, np.float32).reshape(-1, 6)
         n = oceans.shape[0]
+        lam = np.broadcast_to(np.asarray(choppiness, np.float32), (n,))  # a scalar, or one lambda per state
         ps = (L.OceanParams * max(n, 1))()
         for i in range(n):
             o = oceans[i]
-            ps[i] = L.OceanParams(o[0], o[1], o[2], o[3], o[4], o[5], self.texturesSize, choppiness)
+            ps[i] = L.OceanParams(o[0], o[1], o[2], o[3], o[4], o[5], self.texturesSize, float(lam[i]))
         sd = None
         if seeds is not None:
             s = np.ascontiguousarray(seeds, np.uint64)

@@ -2,7 +2,7 @@
  * hlsl_compat.h -- just enough HLSL for the reference's four water compute shaders to compile
  * as C++ ("Oracle A").  TEST INFRASTRUCTURE ONLY.
  *
- * oracle/build_ref.sh streams each .compute file from /root/reference through sed
+ * oracle/Makefile, target `ref` streams each .compute file from /root/reference through sed
  * (strip [numthreads]/semantics, add the `f` suffix HLSL implies on float literals) straight
  * into g++; no reference source is copied into the repo.  This header supplies the vector
  * types with swizzles, texture/buffer objects with operator[], and fp32 intrinsics.

@@ -6,9 +6,9 @@
  * there only as the checker (or as the timed CPU baseline), never as the thing shipped.
  *
  * Parity pin: the reference (Unity C# + HLSL compute) ships no tests, golden vectors or
- * fixtures, so this transcription is pinned by "Oracle A" (oracle/build_ref.sh): the reference's
+ * fixtures, so this transcription is pinned by "Oracle A" (oracle/Makefile, target `ref`): the reference's
  * own .compute shader text compiled as C++ through oracle/hlsl_compat.h and replayed in the
- * WaterBody.cs / IFFT.cs dispatch order.  tests/test_oracle_pin.py requires A == B bit-for-bit,
+ * WaterBody.cs / IFFT.cs dispatch order.  tests/test_oracle.py::test_oracle_a_equals_oracle_b requires A == B bit-for-bit,
  * and tests/golden/ holds vectors generated from Oracle A.
  *
  * The transcription follows the reference op for op; citations are file:line into /root/reference

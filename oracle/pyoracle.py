@@ -218,3 +218,88 @@ class OracleA:
             self.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------------------------
+# Oracle A for the array consumers (oracle/surface_ref_host.cpp + the reference's own lines of
+# Water.shader / WaterBody.cs / BuoyantObject.cs, built by `make -C oracle ref`).
+LIB_S = os.path.join(HERE, "_ref", "libsurface_ref.so")
+_libS = None
+
+
+def have_surface_ref():
+    return os.path.exists(LIB_S)
+
+
+def _load_s():
+    global _libS
+    if _libS is None:
+        if not os.path.exists(LIB_S):
+            raise RuntimeError("surface Oracle A (oracle/_ref/libsurface_ref.so) has not been built")
+        L = ctypes.CDLL(LIB_S)
+        i, f = ctypes.c_int, ctypes.c_float
+        L.surface_ref_domain.argtypes = [_fp, i, i, _fp, _fp, i, f, _fp]
+        L.surface_ref_fragment.argtypes = [_fp, _fp, _fp, _fp, i, i, _fp, _fp, i, f, _fp, _fp]
+        L.surface_ref_get_water_height.argtypes = [_fp, i, _fp, i, _fp]
+        L.surface_ref_buoyancy.argtypes = [_fp, i, _fp, i, f, f, _fp]
+        _libS = L
+    return _libS
+
+
+def _f32(a):
+    a = np.ascontiguousarray(a, np.float32)
+    return a, a.ctypes.data_as(_fp)
+
+
+def pack_mips(levels_per_layer):
+    """[layer][level0, level1, ...] -> the packed chain layout of the library: [layer][level 1 | level 2 | ...]."""
+    return np.concatenate([np.concatenate([lv.reshape(-1, 4) for lv in levels[1:]]) for levels in levels_per_layer]).astype(np.float32)
+
+
+def surface_ref_domain(disp, wavelengths, pts, lod=0.0):
+    """Water.shader:322-326 (reference text) -> displacement [n][3]."""
+    d, dp = _f32(disp)
+    w, wp = _f32(wavelengths)
+    p, pp = _f32(np.asarray(pts, np.float32).reshape(-1, 2))
+    out = np.empty((p.shape[0], 3), np.float32)
+    _load_s().surface_ref_domain(dp, d.shape[1], d.shape[0], wp, pp, p.shape[0], float(lod), out.ctypes.data_as(_fp))
+    return out
+
+
+def surface_ref_fragment(deriv, deriv_mips, turb, turb_mips, wavelengths, pts, lod=0.0):
+    """Water.shader:337-347 (reference text) -> (normalOS [n][3], turbulence sum [n]).  *_mips: packed chains or None."""
+    d, dp = _f32(deriv)
+    t, tp = _f32(turb)
+    dm = tm = None
+    dmp = tmp = None
+    if deriv_mips is not None:
+        dm, dmp = _f32(deriv_mips)
+        tm, tmp = _f32(turb_mips)
+    w, wp = _f32(wavelengths)
+    p, pp = _f32(np.asarray(pts, np.float32).reshape(-1, 2))
+    normal, foam = np.empty((p.shape[0], 3), np.float32), np.empty(p.shape[0], np.float32)
+    _load_s().surface_ref_fragment(dp, dmp, tp, tmp, d.shape[1], d.shape[0], wp, pp, p.shape[0], float(lod),
+                                   normal.ctypes.data_as(_fp), foam.ctypes.data_as(_fp))
+    return normal, foam
+
+
+def surface_ref_get_water_height(layer0, pts):
+    """WaterBody.GetWaterHeight WB:195-209 (reference text).  layer0 [N][N][4] or None (no readback yet)."""
+    p, pp = _f32(np.asarray(pts, np.float32).reshape(-1, 2))
+    out = np.empty(p.shape[0], np.float32)
+    if layer0 is None:
+        _load_s().surface_ref_get_water_height(None, 0, pp, p.shape[0], out.ctypes.data_as(_fp))
+    else:
+        a, ap = _f32(layer0)
+        _load_s().surface_ref_get_water_height(ap, a.shape[0], pp, p.shape[0], out.ctypes.data_as(_fp))
+    return out
+
+
+def surface_ref_buoyancy(layer0, boxes, density=1.0, gravity_y=-9.81):
+    """BuoyantObject.FixedUpdate BO:17-37 (reference text) over WaterBody.GetWaterHeight (reference text):
+    [n][2] = (waterHeight, y of the buoyant acceleration it applied)."""
+    a, ap = _f32(layer0)
+    b, bp = _f32(np.asarray(boxes, np.float32).reshape(-1, 6))
+    out = np.empty((b.shape[0], 2), np.float32)
+    _load_s().surface_ref_buoyancy(ap, a.shape[0], bp, b.shape[0], float(density), float(gravity_y), out.ctypes.data_as(_fp))
+    return out

@@ -1,6 +1,6 @@
 /*
  * ref_host.cpp -- host replay for "Oracle A": drives the reference's own compute-shader text
- * (compiled as C++ by oracle/build_ref.sh) in the order WaterBody.cs / IFFT.cs dispatch it.
+ * (compiled as C++ by oracle/Makefile, target `ref`) in the order WaterBody.cs / IFFT.cs dispatch it.
  * TEST INFRASTRUCTURE ONLY.  Output: oracle/_ref/libocean_ref.so (git-ignored).
  *
  * The shader translation units keep their uniforms/textures as globals (as HLSL does), so this

@@ -10,10 +10,15 @@ numpy fp32 restatement, operation for operation, of
   - the height lookup behind BuoyantObject.cs:18 -> WaterBody.GetWaterHeight (WaterBody.cs:195-209), extended
     to invert the horizontal displacement of Water.shader:327.
 
-PARITY UNPINNED for this module: the shader stages cannot be executed here (no graphics stack on this
-box) and Unity's mip filter is not part of the reference tree, so the chain is DEFINED as the 2x2 box
-filter.  What is pinned: the arithmetic is checked against closed forms in tests/test_surface_oracle.py,
-and the CUDA kernels (compiled without FMA contraction) are compared with it bit for bit.
+PIN: the arithmetic of Water.shader:322-326 / 337-347, WaterBody.GetWaterHeight (WaterBody.cs:195-209) and
+BuoyantObject.FixedUpdate (BuoyantObject.cs:17-37) is pinned to the reference's own text: `make -C oracle ref`
+streams those lines through sed into g++ (oracle/surface_ref_host.cpp supplies the types) and
+tests/test_surface_oracle.py asserts this module equals that library bit for bit.  What stays UNPINNED, by
+nature: the texture sampler underneath (Unity / driver behaviour: restated here and in surface_ref_host.cpp as
+Repeat + trilinear with texel centres at (i + 0.5)/n) and Unity's mip filter, which is not part of the reference
+tree, so the chain is DEFINED as the 2x2 box filter; the displaced-height inversion is this library's own
+extension (checked against Newton in fp64).  The CUDA kernels (compiled without FMA contraction) are compared
+with this module bit for bit.
 """
 import numpy as np
 

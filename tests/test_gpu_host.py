@@ -1,0 +1,118 @@
+"""GPU tests of the host-side state machine of liboceanfft.so (workspace sharing, staged parameter edits,
+the readback ring across a foam reset, ensemble lambda), through the C ABI."""
+import numpy as np
+import pytest
+
+from test_gpu_parity import check_fields, make_body
+
+pytestmark = pytest.mark.gpu
+
+
+def test_two_geometries_with_equal_bytes_on_one_stream(pkg, po):
+    """512 x 1 and 256 x 4 have the same plane bytes; on one caller stream they must NOT share a workspace
+    (its counters are one per layer and count rows of N texels).  Both oceans, interleaved frame by frame on
+    the stream, must equal the same oceans run on private streams, bit for bit."""
+    import torch
+    cfg = pkg.scene.config(2)
+    one = dict(cfg, cascades=cfg["cascades"][:1])
+    four = dict(cfg, cascades=pkg.scene.SCENE_CASCADES)
+    st = torch.cuda.Stream()
+    a, na = make_body(pkg, po, one, N=512)
+    b, nb = make_body(pkg, po, four, N=256)
+    ra, _ = make_body(pkg, po, one, N=512, noise=na)
+    rb, _ = make_body(pkg, po, four, N=256, noise=nb)
+    a.SetStream(st.cuda_stream)
+    b.SetStream(st.cuda_stream)
+    for f in range(6):
+        t = f / 60.0
+        for x in (a, b, ra, rb):
+            x.CalculateWavesTexturesAtTime(t)
+    for x, r in ((a, ra), (b, rb)):
+        assert np.array_equal(x.displacementsTextures, r.displacementsTextures)
+        assert np.array_equal(x.derivativesTextures, r.derivativesTextures)
+        assert np.array_equal(x.turbulenceTextures, r.turbulenceTextures)
+    # same-geometry handles on the stream still share (and still agree)
+    c, _ = make_body(pkg, po, four, N=256, noise=nb)
+    c.SetStream(st.cuda_stream)
+    for f in range(6):
+        c.CalculateWavesTexturesAtTime(f / 60.0)
+    assert np.array_equal(c.turbulenceTextures, rb.turbulenceTextures)
+    for x in (a, b, c, ra, rb):
+        x.OnDisable()
+
+
+def test_set_params_is_staged_until_the_spectrum_is_recomputed(pkg, po):
+    """ocean_set_params between two frames must not change the second one (new wavelengths with the old h0 /
+    omega would be inconsistent); ocean_init_spectrum commits the edit and the oracle agrees afterwards."""
+    cfg = pkg.scene.config(2)
+    body, noise = make_body(pkg, po, cfg, N=128)
+    twin, _ = make_body(pkg, po, cfg, N=128, noise=noise)
+    body.CalculateWavesTexturesAtTime(0.0)
+    twin.CalculateWavesTexturesAtTime(0.0)
+    wl = body.wavelengths
+    body.windSpeed, body.depth, body.choppiness = 15.0, 35.0, 0.5
+    body.cascades = [pkg.WaterCascade.from_tuple((c[0] * 0.5, c[1], c[2], c[3], c[4])) for c in cfg["cascades"]]
+    body.SetParams()
+    body.CalculateWavesTexturesAtTime(0.1)
+    twin.CalculateWavesTexturesAtTime(0.1)
+    assert body.wavelengths == wl
+    assert np.array_equal(body.displacementsTextures, twin.displacementsTextures)
+    assert np.array_equal(body.turbulenceTextures, twin.turbulenceTextures)
+    pts = np.array([[3.0, -7.0], [250.0, 90.0]], np.float32)
+    assert np.array_equal(body.GetWaterHeights(pts, pkg._lib.QUERY_BILINEAR_ALL_CASCADES),
+                          twin.GetWaterHeights(pts, pkg._lib.QUERY_BILINEAR_ALL_CASCADES))
+    body.CalculateInitialSpectrumTextures()
+    assert body.wavelengths == [np.float32(w * 0.5) for w in wl]
+    casc = [(c[0] * 0.5, c[1], c[2], c[3], c[4]) for c in cfg["cascades"]]
+    ocean = (15.0,) + tuple(cfg["ocean"][1:5]) + (35.0,)
+    ob = po.OracleB(128, ocean, casc, noise)
+    ob.init_spectrum()
+    ob.step(0.2)
+    body.ResetFoam()
+    body.CalculateWavesTexturesAtTime(0.2)
+    want = ob.get(po.DISP).copy()
+    want[..., 0] *= np.float32(0.5)  # lambda = 0.5 scales the horizontal displacement (the oracle is lambda = 1)
+    want[..., 2] *= np.float32(0.5)
+    check_fields(body.displacementsTextures, want, "displacement after the committed edit")
+    body.OnDisable()
+    twin.OnDisable()
+
+
+def test_reset_foam_restarts_the_readback_ring(pkg, po):
+    """After ocean_reset_foam the frame index restarts; READBACK_REF must answer 0 (WB:197) until a
+    post-reset readback completes, then serve it -- not a stale pre-reset layer with a larger frame index."""
+    cfg = pkg.scene.config(1)
+    body, _ = make_body(pkg, po, cfg, N=128)
+    for f in range(5):
+        body.Update(f / 60.0)
+    frame, _ = body.WaitReadback()
+    assert frame == 4
+    assert body.GetWaterHeight((3.0, 0.0, -7.0)) != 0.0
+    body.ResetFoam()
+    assert body.GetWaterHeight((3.0, 0.0, -7.0)) == 0.0
+    assert body.WaitReadback() == (-1, None)
+    body.Update(2.0)
+    frame, data = body.WaitReadback()
+    assert frame == 0
+    assert np.array_equal(data, body.displacementsTextures[0])
+    for f in range(1, 5):  # every slot of the ring is usable again
+        body.Update(2.0 + f / 60.0)
+    frame, data = body.WaitReadback()
+    assert frame == 4 and np.array_equal(data, body.displacementsTextures[0])
+    body.OnDisable()
+
+
+def test_ensemble_rejects_a_wave_with_mixed_lambda(pkg, po):
+    cfg = pkg.scene.config(5)
+    oceans, seeds = pkg.scene.ensemble_states(4)
+    ens = pkg.OceanEnsemble(64, cfg["cascades"], batch=2)
+    with pytest.raises(pkg._lib.OceanError) as e:
+        ens.run(oceans, seeds, time=1.0, choppiness=[1.0, 0.5, 1.0, 1.0])
+    assert e.value.status == pkg._lib.ERR_INVALID_PARAMS and "lambda" in e.value.message
+    # one lambda per wave is fine, and is honoured per wave
+    mixed = ens.run(oceans, seeds, time=1.0, choppiness=[1.0, 1.0, 0.5, 0.5])
+    ones = ens.run(oceans, seeds, time=1.0, choppiness=1.0)
+    halves = ens.run(oceans, seeds, time=1.0, choppiness=0.5)
+    assert mixed[:2].tolist() == ones[:2].tolist() and mixed[2:].tolist() == halves[2:].tolist()
+    assert mixed[2:].tolist() != ones[2:].tolist()
+    ens.close()

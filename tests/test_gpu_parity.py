@@ -156,7 +156,7 @@ def test_config3_headline_shape(pkg, po):
 
 def test_config2_foam_accumulation(pkg, po):
     """BASELINE config 2 (scene defaults, 3 cascades x 256^2): foam recursion over many frames.
-    The oracle is run for 60 frames here (the full 600 are a size-independent property below)."""
+    The oracle is run for 60 frames here; test_config2_all_600_frames_against_the_oracle runs all 600."""
     cfg = pkg.scene.config(2)
     body, noise = make_body(pkg, po, cfg)
     ob = po.OracleB(cfg["N"], cfg["ocean"], cfg["cascades"], noise, threads=0)
@@ -173,7 +173,6 @@ def test_config2_foam_accumulation(pkg, po):
     # 600-frame property: foam_n = e^-2 foam_{n-1} (+ J if below J)  =>  J <= foam <= J / (1 - e^-2) wherever J > 0
     for f in range(60, 600):
         body.CalculateWavesTexturesAtTime(cfg["times"][f])
-    d = body.derivativesTextures.astype(np.float64)
     turb = body.turbulenceTextures[..., 0].astype(np.float64)
     assert np.isfinite(turb).all()
     assert turb.max() <= 50.0  # bounded: no blow-up over 600 frames
@@ -574,3 +573,88 @@ def test_sharded_ensemble_on_one_gpu(pkg, po):
     parts = [pkg.sharding.run_sharded(lambda oc, sd: ens.run(oc, sd, time=1.0), oceans, seeds, r, 2) for r in range(2)]
     assert np.array_equal(parts[0] + parts[1], full)  # disjoint rows, zero elsewhere
     ens.close()
+
+
+def test_config4_matches_oracle_with_queries(pkg, po):
+    """BASELINE config 4 as specified: 4 cascades x 1024^2, scene ocean, seed 4 -- the regime where the
+    row->column workspace (134 MB) exceeds L2 and four layers go through the 544-thread TMA column kernel
+    and its per-layer counters -- three frames against Oracle B (WB:180-193, IFFT.cs:66-94), then the
+    1 M query points of the config (seed 40) in NEAREST_REF: bit-exact against the numpy restatement of
+    WB:199-208 on the library's own displacement, and within tolerance of OracleB.query_heights."""
+    cfg = pkg.scene.config(4)
+    N = cfg["N"]
+    assert N == 1024 and len(cfg["cascades"]) == 4
+    body, noise = make_body(pkg, po, cfg)
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    for c in range(4):
+        assert rel_l2(body.initialSpectrumTextures[c], ob.get(po.H0)[c]) <= TOL_SPECTRUM_L2
+    for f in range(3):
+        ob.step(cfg["times"][f])
+        body.CalculateWavesTexturesAtTime(cfg["times"][f])
+    disp = body.displacementsTextures
+    check_fields(disp, ob.get(po.DISP), "config4 displacement")
+    check_fields(body.derivativesTextures, ob.get(po.DERIV), "config4 derivatives")
+    check_turbulence(body.turbulenceTextures, ob.get(po.TURB))
+    rng = np.random.default_rng(cfg["query_seed"])
+    pts = rng.uniform(-N / 2, N / 2, (cfg["query_points"], 2)).astype(np.float32)
+    got = body.GetWaterHeights(pts, pkg._lib.QUERY_NEAREST_REF)
+    lo, hi = np.float32(-(N // 2)), np.float32(N // 2)
+    u = np.clip((pts[:, 0] - lo) / (hi - lo), np.float32(0), np.float32(1)).astype(np.float32)
+    v = np.clip((pts[:, 1] - lo) / (hi - lo), np.float32(0), np.float32(1)).astype(np.float32)
+    x = np.clip((u * np.float32(N)).astype(np.int32), 0, N - 1)
+    y = np.clip((v * np.float32(N)).astype(np.int32), 0, N - 1)
+    assert np.array_equal(got, disp[0][y, x, 1])
+    want = ob.query_heights(pts)
+    assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max()
+    body.OnDisable()
+
+
+def test_config2_all_600_frames_against_the_oracle(pkg, po):
+    """BASELINE config 2 in full: the foam recursion RF:28-32 over all 600 frames (t_f = f / 60) against
+    Oracle B, turbulence checked with the branch-flip rule at frames 60 / 200 / 400 / 600 and the fields at
+    the end.  A flipped texel differs by O(J) and decays by e^-2 per frame, so flips do not accumulate."""
+    cfg = pkg.scene.config(2)
+    body, noise = make_body(pkg, po, cfg)
+    ob = po.OracleB(cfg["N"], cfg["ocean"], cfg["cascades"], noise, threads=0)
+    ob.init_spectrum()
+    flips = []
+    for f in range(600):
+        ob.step(cfg["times"][f])
+        body.CalculateWavesTexturesAtTime(cfg["times"][f])
+        if f + 1 in (60, 200, 400, 600):
+            flips.append(check_turbulence(body.turbulenceTextures, ob.get(po.TURB)))
+    check_fields(body.displacementsTextures, ob.get(po.DISP), "displacement after 600 frames")
+    check_fields(body.derivativesTextures, ob.get(po.DERIV), "derivatives after 600 frames")
+    assert body.frame == 600
+    turb = body.turbulenceTextures[..., 0].astype(np.float64)
+    assert np.isfinite(turb).all() and turb.max() <= 50.0
+    body.OnDisable()
+
+
+def test_default_ensemble_path_at_config5_size_matches_oracle(pkg, po):
+    """The default (separate spectrum kernel, two lanes) ensemble path at the size config 5 runs:
+    3 cascades x 512^2, three randomised states in waves of two, every array of two states against Oracle B."""
+    cfg = pkg.scene.config(5)
+    N = cfg["N"]
+    assert N == 512 and len(cfg["cascades"]) == 3
+    oceans, seeds = pkg.scene.ensemble_states(3, cfg["rng_seed"])
+    with _ensemble_env(None):
+        ens = pkg.OceanEnsemble(N, cfg["cascades"], batch=2)
+        whole = pkg.OceanEnsemble(N, cfg["cascades"], batch=3)
+    sums = ens.run(oceans, seeds, time=cfg["time"])
+    assert sums.tolist() == whole.run(oceans, seeds, time=cfg["time"]).tolist()
+    ids = (pkg._lib.DISPLACEMENT, pkg._lib.DERIVATIVES, pkg._lib.TURBULENCE)
+    for i in (0, 2):
+        got = [whole.copy_output(w, i) for w in ids]
+        for k in range(3):
+            assert int(got[k].view(np.uint32).astype(np.uint64).sum()) == int(sums[i, k])
+        ob = po.OracleB(N, tuple(float(v) for v in oceans[i]), cfg["cascades"], po.fill_noise(int(seeds[i]), N), threads=0)
+        ob.init_spectrum()
+        ob.step(cfg["time"])
+        check_fields(got[0], ob.get(po.DISP), "ensemble state %d displacement" % i)
+        check_fields(got[1], ob.get(po.DERIV), "ensemble state %d derivatives" % i)
+        check_turbulence(got[2], ob.get(po.TURB))
+        ob.close()
+    ens.close()
+    whole.close()

@@ -123,3 +123,103 @@ def test_buoyancy_oracle_closed_forms():
     assert np.allclose(out[1], [1.0, 11.0, 10.0 * 2.0 * 6.0, 6.0])
     assert np.array_equal(out[2], np.array([3.5, 0.0, 0.0, 0.0], np.float32))
     assert out.dtype == np.float32
+
+
+# ---- the pin: oracle/surface_oracle.py == the reference's own lines compiled here (oracle/_ref/libsurface_ref.so) ----
+# Water.shader:322-326 / 337-347 (HLSL) and WaterBody.cs:195-209 / BuoyantObject.cs:17-37 (C#) are streamed through sed
+# into g++ by `make -C oracle ref`; only the texture sampler underneath them is a restatement (Unity / driver behaviour).
+
+def _pin():
+    from oracle import pyoracle as po
+    if not po.have_surface_ref():
+        if not __import__("os").path.isdir("/root/reference"):
+            pytest.skip("oracle/_ref/libsurface_ref.so was not built (no /root/reference here)")
+        po.build(ref=True)
+    return po
+
+
+def _random_ocean_arrays(seed, C, N):
+    rng = np.random.default_rng(seed)
+    disp = rng.standard_normal((C, N, N, 4)).astype(F)
+    disp[..., 3] = 0
+    deriv = (0.3 * rng.standard_normal((C, N, N, 4))).astype(F)
+    turb = np.repeat(rng.uniform(-0.5, 1.8, (C, N, N, 1)).astype(F), 4, axis=3)  # straddles both saturate() bounds
+    return disp, deriv, turb
+
+
+@pytest.mark.parametrize("lod", [0.0, 0.75, 2.0, 3.5, 99.0])
+def test_surface_oracle_equals_the_reference_shader_lines(lod):
+    po = _pin()
+    C, N = 3, 32
+    disp, deriv, turb = _random_ocean_arrays(7, C, N)
+    wl = np.array([1530.0, 201.0, 34.0], F)
+    rng = np.random.default_rng(8)
+    pts = rng.uniform(-4000, 4000, (5000, 2)).astype(F)
+    pts[:4] = [[0, 0], [-0.0, 1530.0], [100.5, -17.0], [1e6, -1e6]]
+    want_d, want_n, want_f = so.surface(disp, deriv, turb, wl, pts, lod=lod, mips=True)
+    dm = po.pack_mips([so.mip_chain(deriv[c]) for c in range(C)])
+    tm = po.pack_mips([so.mip_chain(turb[c]) for c in range(C)])
+    got_d = po.surface_ref_domain(disp, wl, pts, lod)
+    got_n, got_f = po.surface_ref_fragment(deriv, dm, turb, tm, wl, pts, lod)
+    assert np.array_equal(got_d.view(np.uint32), want_d.view(np.uint32))
+    assert np.array_equal(got_n.view(np.uint32), want_n.view(np.uint32))
+    assert np.array_equal(got_f.view(np.uint32), want_f.view(np.uint32))
+    # a texture without a chain reads level 0 at every LOD
+    want_d0, want_n0, want_f0 = so.surface(disp, deriv, turb, wl, pts, lod=lod, mips=False)
+    got_n0, got_f0 = po.surface_ref_fragment(deriv, None, turb, None, wl, pts, lod)
+    assert np.array_equal(got_n0.view(np.uint32), want_n0.view(np.uint32)) and np.array_equal(got_f0, want_f0)
+
+
+def _numpy_get_water_height(layer0, pts):
+    """WB:199-208 in numpy fp32 -- the restatement the GPU tests compare OCEAN_QUERY_NEAREST_REF with."""
+    N = layer0.shape[0]
+    lo, hi = F(-(N // 2)), F(N // 2)
+    u = np.clip((pts[:, 0] - lo) / (hi - lo), F(0), F(1)).astype(F)
+    v = np.clip((pts[:, 1] - lo) / (hi - lo), F(0), F(1)).astype(F)
+    x = np.clip((u * F(N)).astype(np.int32), 0, N - 1)
+    y = np.clip((v * F(N)).astype(np.int32), 0, N - 1)
+    return layer0[y, x, 1]
+
+
+def test_get_water_height_and_buoyancy_equal_the_reference_csharp_lines():
+    po = _pin()
+    N = 64
+    disp, _, _ = _random_ocean_arrays(9, 1, N)
+    rng = np.random.default_rng(10)
+    pts = rng.uniform(-N / 2 - 6, N / 2 + 6, (20000, 2)).astype(F)
+    pts[:8] = [[-N / 2, -N / 2], [N / 2, N / 2], [0, 0], [-1e9, 1e9], [N / 2 - 1e-3, 0], [0.5, -0.5], [-0.0, 0.0], [31.99999, -32.0]]
+    got = po.surface_ref_get_water_height(disp[0], pts)
+    assert np.array_equal(got, _numpy_get_water_height(disp[0], pts))
+    # ... and Oracle B's transcription of the same method (oracle/ocean_oracle.hpp) agrees bit for bit
+    assert np.array_equal(po.surface_ref_get_water_height(None, pts), np.zeros(len(pts), F))  # WB:197: no readback yet
+    # BuoyantObject.FixedUpdate over it: boxes straddling the surface, zero and huge scales
+    boxes = np.empty((len(pts), 6), F)
+    boxes[:, 0], boxes[:, 2] = pts[:, 0], pts[:, 1]
+    boxes[:, 1] = rng.uniform(-3, 3, len(pts))
+    boxes[:, 3:] = rng.uniform(0.05, 4.0, (len(pts), 3))
+    boxes[:3, 4] = [1e-30, 1e30, 0.5]
+    for density, g in ((1.0, -1.0), (1.0, -9.81), (0.7, 3.5)):
+        want = so.buoyancy(_numpy_get_water_height(disp[0], pts), boxes, density=density, gravity_y=g)
+        got = po.surface_ref_buoyancy(disp[0], boxes, density=density, gravity_y=g)
+        assert np.array_equal(got[:, 0].view(np.uint32), want[:, 0].view(np.uint32))  # waterHeight   BO:18
+        assert np.array_equal(got[:, 1].view(np.uint32), want[:, 2].view(np.uint32))  # |g.y| * (density * submergedVolume)  BO:26-29
+        assert (want[:, 1] > 0).sum() > 1000 and (want[:, 1] == 0).sum() > 1000
+    # density = |g.y| = 1 makes the applied acceleration the submerged volume itself (BO:25)
+    want = so.buoyancy(_numpy_get_water_height(disp[0], pts), boxes, density=1.0, gravity_y=-1.0)
+    got = po.surface_ref_buoyancy(disp[0], boxes, density=1.0, gravity_y=-1.0)
+    assert np.array_equal(got[:, 1].view(np.uint32), want[:, 3].view(np.uint32))
+
+
+def test_oracle_b_query_equals_the_reference_get_water_height(po):
+    """Oracle B's hand transcription of GetWaterHeight == WB:195-209 compiled from the reference text."""
+    pin = _pin()
+    import oceanpkg
+    cfg = oceanpkg.load().scene.config(1)
+    N = 64
+    noise = po.fill_noise(1, N)
+    ob = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise)
+    ob.init_spectrum()
+    ob.step(1.0)
+    rng = np.random.default_rng(40)
+    pts = rng.uniform(-N / 2 - 4, N / 2 + 4, (5000, 2)).astype(F)
+    assert np.array_equal(ob.query_heights(pts), pin.surface_ref_get_water_height(ob.get(po.DISP)[0], pts))
