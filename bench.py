@@ -9,9 +9,16 @@ Workload at every N: BASELINE config 3 -- 4 cascades x 512^2, depth 20 m, swell 
 inverse FFTs + assembly) of one ocean.  Weak scaling: every rank runs its own independent oceans,
 no collective on the data path; value = frames of all ranks x 4 cascades / max-over-ranks time.
 L2 hygiene: the timed loop rotates over several ocean instances so that the working set
-(~117 MB each) exceeds the 126 MB L2 -- see config.l2.
+(~76 MB each) exceeds the 126 MB L2 -- see config.l2.
+
+Timed region (value): W warm-up frames, device sync + rank barrier, then PRIME frames issued on the stream
+immediately before the start event with no sync in between, then EXACTLY K frames, the stop event, and a
+device sync + rank barrier.  The priming frames keep the GPU busy and the host ahead of it when the start
+event is reached, so the K frames are steady-state pipelined frames even for a small K; nothing is moved
+out of the timed region (every frame still runs both kernels over all four cascades).
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -28,8 +35,30 @@ if ROOT not in sys.path:
 METRIC = "cascade_frames_per_sec"
 UNIT = "cascade-frames/s"
 WORKLOAD = "config3: 4 cascades x 512^2, U10=10 m/s, fetch=100 km, depth=20 m (TMA), swell=0.8, all outputs"
-ALG_BYTES_PER_TEXEL_CASCADE = 96  # h0 16 + waveData 16 + turbulence 16 in, 3 x 16 out
-INSTANCES = int(os.environ.get("OCEAN_BENCH_INSTANCES", "4"))  # rotated per step: 4 x ~117 MB working set > 126 MB L2
+ALG_BYTES_PER_TEXEL_CASCADE = 96   # h0 16 + waveData 16 + turbulence 16 in, 3 x 16 out (the contract's numerator)
+BUILT_BYTES_PER_TEXEL_CASCADE = 88  # what this build must move: it reads the 8-byte (1/|k|, omega) copy instead of waveData
+INSTANCES = int(os.environ.get("OCEAN_BENCH_INSTANCES", "4"))  # rotated per step: 4 x ~76 MB of inputs + outputs > 126 MB L2
+PRIME = int(os.environ.get("OCEAN_BENCH_PRIME", "12"))         # pipeline-priming frames right before the start event
+BOXES = 4096                                                     # buoyant boxes per frame on the query path (96 KiB in, 64 KiB out)
+# One `config` for both arms (the driver compares them): the workload and how the metric is taken.
+CONFIG = {
+    "workload": WORKLOAD,
+    "N": 512, "cascades": 4, "time_base": "t_f = f / 60 s",
+    "sharding": "independent ocean instances per GPU, no collective on the data path",
+    "l2": "cuda arm: the timed loop rotates over %d ocean instances on one stream (%.0f MB of inputs + outputs > 126 MB L2; "
+          "the 33.5 MB row->column workspace is shared per stream and stays in L2 by design); reference arm: host caches, n/a"
+          % (INSTANCES, INSTANCES * (16 + 8 + 48) * 512 * 512 * 4 / 1e6),
+}
+KERNEL_SOURCES = ["ocean_frame.cu", "ocean_fft.cuh", "ocean_fused.cuh", "ocean_evolve.cuh", "ocean_tma.cuh", "ocean_internal.h"]
+
+
+def kernel_source_hash():
+    """sha256 over the frame-kernel sources: profiles/traffic.json carries the hash of the build it was measured on."""
+    h = hashlib.sha256()
+    for name in KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "ocean-simulation_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
 
 
 class ClockSampler(threading.Thread):
@@ -78,20 +107,23 @@ def workload(pkg):
     return cfg, cfg["N"], len(cfg["cascades"])
 
 
-def cpu_reference(steps, warmup, max_seconds=None):
-    """Times the reference's own kernels (Oracle A: its .compute text compiled as C++, oracle/_ref) on all
-    host cores; falls back to the hand port (Oracle B) when oracle/_ref was not built.  Checker code is
-    executed here only as the measured CPU baseline."""
+def _oracle(po, N, cfg, noise, threads):
+    """Oracle A (the reference's .compute text compiled as C++, oracle/_ref) when it was built, else the hand port."""
+    if po.have_ref():
+        return po.OracleA(N, cfg["ocean"], cfg["cascades"], noise, threads=threads), "reference"
+    return po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=threads), "port"
+
+
+def cpu_reference(steps, warmup, max_seconds=None, threads=None):
+    """Times the reference's own kernels (Oracle A; Oracle B when oracle/_ref was not built) on `threads` host
+    threads (default: all).  Checker code is executed here only as the measured CPU baseline."""
     import oceanpkg
     from oracle import pyoracle as po
     pkg = oceanpkg.load()
     cfg, N, C = workload(pkg)
     noise = po.fill_noise(cfg["seed"], N)
-    cores = os.cpu_count() or 1
-    if po.have_ref():
-        o, kind = po.OracleA(N, cfg["ocean"], cfg["cascades"], noise, threads=cores), "reference"
-    else:
-        o, kind = po.OracleB(N, cfg["ocean"], cfg["cascades"], noise, threads=cores), "port"
+    cores = threads or os.cpu_count() or 1
+    o, kind = _oracle(po, N, cfg, noise, cores)
     o.init_spectrum()
     for f in range(warmup):
         o.step(f / 60.0)
@@ -100,35 +132,78 @@ def cpu_reference(steps, warmup, max_seconds=None):
     for f in range(steps):
         o.step((warmup + f) / 60.0)
         done += 1
-        if max_seconds is not None and time.perf_counter() - t0 > max_seconds and done >= 3:
+        if max_seconds is not None and time.perf_counter() - t0 > max_seconds and done >= 2:
             break
     dt = time.perf_counter() - t0
     o.close()
     return {"value": C * done / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "%d frames of %s (%s, OpenMP over texel rows, %d threads)" % (
-                done, WORKLOAD, "reference .compute text compiled as C++" if kind == "reference" else "C++ transcription", cores),
+            "sample": "%d frames of %s (%s, OpenMP over texel rows, %d thread%s)" % (
+                done, WORKLOAD, "reference .compute text compiled as C++" if kind == "reference" else "C++ transcription",
+                cores, "" if cores == 1 else "s"),
             "ms_per_step": 1e3 * dt / done, "steps": done}
+
+
+def cpu_config1():
+    """BASELINE config 1 on the CPU: InitialSpectrum + one frame (time evolution + IFFT + assembly) of 1 x 256^2,
+    single thread and all threads, best of 3 ('config 1: CPU transcription ... parity + CPU timing')."""
+    import oceanpkg
+    from oracle import pyoracle as po
+    pkg = oceanpkg.load()
+    cfg = pkg.scene.config(1)
+    N = cfg["N"]
+    noise = po.fill_noise(cfg["seed"], N)
+    out = {"what": "config 1: 1 cascade x 256^2, InitialSpectrum + one frame at t = 1 s on the host, best of 3"}
+    for label, th in (("single_thread_ms", 1), ("all_threads_ms", os.cpu_count() or 1)):
+        best = None
+        for _ in range(3):
+            o, kind = _oracle(po, N, cfg, noise, th)
+            t0 = time.perf_counter()
+            o.init_spectrum()
+            o.step(1.0)
+            dt = time.perf_counter() - t0
+            o.close()
+            best = dt if best is None else min(best, dt)
+        out[label] = 1e3 * best
+        out["kind"] = kind
+    out["cores"] = os.cpu_count() or 1
+    return out
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_reference(args.steps, min(args.warmup, 2))
+    r = cpu_reference(args.steps, args.warmup)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": r["steps"], "warmup": min(args.warmup, 2), "ms_per_step": r["ms_per_step"],
+            "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "device": "host CPU"},
+            "config": CONFIG, "device": "host CPU",
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def measured_traffic():
+    """dram__bytes_read + dram__bytes_write per frame from profiles/traffic.json -- only if it was measured on THIS build
+    of the frame kernels (the file carries the hash of the sources it was taken on)."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tpath):
+        return None, "profiles/traffic.json missing"
+    with open(tpath) as f:
+        t = json.load(f)
+    here = kernel_source_hash()
+    if t.get("source_hash") != here:
+        return None, "profiles/traffic.json is stale: measured on kernel sources %s, this build is %s" % (t.get("source_hash"), here)
+    return t.get("frame_dram_bytes"), "ncu dram__bytes_read.sum + dram__bytes_write.sum per frame (rows + cols), %s, kernel sources %s" % (
+        t.get("how", "profiles/traffic.json"), here)
 
 
 def run_cuda(args):
     import torch
     import oceanpkg
     pkg = oceanpkg.load()
-    lib = pkg._lib.load()
+    L = pkg._lib
+    lib = L.load()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -139,6 +214,8 @@ def run_cuda(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sampler = ClockSampler(local)  # started before the warm-up: it covers every timed region below
+    sampler.start()
     cfg, N, C = workload(pkg)
     o = cfg["ocean"]
     stream = torch.cuda.Stream(device=local)  # a real (non-NULL) stream shared by torch events and the library
@@ -149,6 +226,7 @@ def run_cuda(args):
                           texturesSize=N, cascades=cfg["cascades"], seed=1000 * rank + cfg["seed"] + i, device=local).Awake()
         b.SetStream(stream.cuda_stream)  # torch events then bracket exactly the library's launches
         bodies.append(b)
+    copy_streams = [torch.cuda.ExternalStream(b.copyStream, device=local) for b in bodies]
 
     def barrier():
         torch.cuda.synchronize()
@@ -156,108 +234,222 @@ def run_cuda(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    K, W = args.steps, max(args.warmup, 3)
-    for f in range(W):
-        bodies[f % INSTANCES].CalculateWavesTexturesAtTime(f / 60.0)
+    def reduce_max(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        t = torch.tensor(vals, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t]
+
+    K, W = args.steps, args.warmup
+    prime = max(PRIME, 3 - W)
+    clock = [0]  # frame counter: t_f = f / 60
+
+    def tick():
+        clock[0] += 1
+        return clock[0] - 1, (clock[0] - 1) / 60.0
+
+    # ---- value: K frames, inputs resident in HBM, device-timed, steady state ----
+    for _ in range(W):
+        f, t = tick()
+        bodies[f % INSTANCES].CalculateWavesTexturesAtTime(t)
     barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
-    time.sleep(0.3)
-    # ---- value: K frames, inputs resident in HBM, device-timed ----
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(prime):
+        f, t = tick()
+        bodies[f % INSTANCES].CalculateWavesTexturesAtTime(t)
     launches0 = lib.ocean_launch_count()
-    barrier()
     e0.record(stream)
-    for f in range(K):
-        bodies[f % INSTANCES].CalculateWavesTexturesAtTime((W + f) / 60.0)
+    for _ in range(K):
+        f, t = tick()
+        bodies[f % INSTANCES].CalculateWavesTexturesAtTime(t)
     e1.record(stream)
-    barrier()
     launches = int(lib.ocean_launch_count() - launches0)
+    barrier()
     ms = e0.elapsed_time(e1)
-    # ---- e2e: WaterBody.Update = frame + async readback to pinned host memory (WB:284-297), through the C ABI.
-    # Timed twice: shipping only the height channel GetWaterHeight consumes (headline), and the reference's
-    # whole-layer RGBA request.
-    def run_e2e(mode, base):
-        for b in bodies:
-            b.SetReadbackMode(mode)
+
+    # ---- e2e through the C ABI with HOST buffers.  Two shapes of WaterBody.Update (WB:284-297):
+    #  query: ocean_update_buoyancy -- the frame, then BuoyantObject.FixedUpdate (BO:18-30) for BOXES boxes answered on the
+    #         owning GPU: boxes travel in from pinned host memory, answers travel back (the headline e2e);
+    #  plane: ocean_update -- the frame + the reference's own readback of displacement layer 0 to pinned host memory
+    #         (HEIGHT: only the channel GetWaterHeight reads, 1 MiB; RGBA: the whole layer as WB:288 requests it, 4 MiB).
+    # Device-timed like `value`: start event on the compute stream after the priming calls, stop = the latest of the
+    # compute stream and every handle's copy stream (where the last answer / readback lands).
+    rng = np.random.default_rng(100 + rank)
+    RING = 4  # in-flight host buffers per handle (the library's readback ring is 3 deep)
+    h_boxes = torch.empty((INSTANCES, RING, BOXES, 6), dtype=torch.float32).pin_memory()
+    h_out = torch.zeros((INSTANCES, RING, BOXES, 4), dtype=torch.float32).pin_memory()
+    bx = np.empty((BOXES, 6), np.float32)
+    bx[:, 0] = rng.uniform(-N / 2, N / 2, BOXES)
+    bx[:, 2] = rng.uniform(-N / 2, N / 2, BOXES)
+    bx[:, 1] = rng.uniform(-1.0, 1.0, BOXES)
+    bx[:, 3:] = rng.uniform(0.5, 2.0, (BOXES, 3))
+    h_boxes[:] = torch.from_numpy(bx)
+
+    def e2e_step(mode):
+        f, t = tick()
+        i, r = f % INSTANCES, (f // INSTANCES) % RING
+        if mode == "query":
+            bodies[i].UpdateBuoyancy(t, (h_boxes[i, r].data_ptr(), BOXES), (h_out[i, r].data_ptr(),), density=1.0, gravityY=-9.81)
+        else:
+            bodies[i].Update(t)
+
+    def run_e2e(mode):
+        if mode != "query":
+            for b in bodies:
+                b.SetReadbackMode(L.READBACK_HEIGHT if mode == "height" else L.READBACK_RGBA)
+        for _ in range(max(W, 3)):
+            e2e_step(mode)
         barrier()
+        s0 = torch.cuda.Event(enable_timing=True)
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(INSTANCES + 1)]
+        for _ in range(prime):
+            e2e_step(mode)
         t0 = time.perf_counter()
-        for f in range(K):
-            bodies[f % INSTANCES].Update((base + f) / 60.0)
+        s0.record(stream)
+        for _ in range(K):
+            e2e_step(mode)
+        ends[INSTANCES].record(stream)
+        for i, cs in enumerate(copy_streams):
+            ends[i].record(cs)
         for b in bodies:
             b.Sync()
         torch.cuda.synchronize()
-        return time.perf_counter() - t0
-    L = pkg._lib
-    run_e2e(L.READBACK_HEIGHT, W + K)  # warm the readback path (pinned buffers, events)
-    e2e_s = run_e2e(L.READBACK_HEIGHT, W + 2 * K)
-    e2e_rgba_s = run_e2e(L.READBACK_RGBA, W + 3 * K)
+        wall = time.perf_counter() - t0
+        barrier()
+        return max(s0.elapsed_time(e) for e in ends), wall * 1e3
+
+    q_ms, q_wall = run_e2e("query")
+    q_check = float(h_out[0, 0, :, 0].abs().sum())  # the answers did arrive in host memory
+    h_ms, h_wall = run_e2e("height")
+    r_ms, r_wall = run_e2e("rgba")
+
+    # ---- the box's device->host ceiling for the plane path: plain cudaMemcpyAsync of 1 MiB blocks, every rank at once ----
+    blocks, reps = 8, 256
+    d_blk = torch.zeros((blocks, N * N), dtype=torch.float32, device="cuda")
+    h_blk = torch.empty((blocks, N * N), dtype=torch.float32).pin_memory()
+    cstream = torch.cuda.Stream(device=local)
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(cstream):
+        for i in range(blocks):
+            h_blk[i].copy_(d_blk[i], non_blocking=True)
+    barrier()
+    with torch.cuda.stream(cstream):
+        c0.record(cstream)
+        for i in range(reps):
+            h_blk[i % blocks].copy_(d_blk[i % blocks], non_blocking=True)
+        c1.record(cstream)
+    barrier()
+    d2h_ms = c0.elapsed_time(c1)
     clocks = sampler.summary()
-    # ---- per-kernel durations (separate pass: an event between the two launches) ----
+
+    # ---- per-kernel durations (separate pass: an event between the two launches, so no overlap) ----
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
     barrier()
-    for f in range(K):
+    for k in range(K):
+        f, t = tick()
         b = bodies[f % INSTANCES]
-        evs[f][0].record(stream)
-        b.StepPartial((W + 4 * K + f) / 60.0, 1)
-        evs[f][1].record(stream)
-        b.StepPartial((W + 4 * K + f) / 60.0, 2)
-        evs[f][2].record(stream)
+        evs[k][0].record(stream)
+        b.StepPartial(t, 1)
+        evs[k][1].record(stream)
+        b.StepPartial(t, 2)
+        evs[k][2].record(stream)
     torch.cuda.synchronize()
     rows_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
     cols_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
-
-    t_ms, t_e2e, t_e2e_rgba = ms, e2e_s, e2e_rgba_s
-    if dist is not None:
-        t = torch.tensor([ms, e2e_s * 1e3, e2e_rgba_s * 1e3], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_ms, t_e2e, t_e2e_rgba = float(t[0]), float(t[1]) / 1e3, float(t[2]) / 1e3
     describe = bodies[0].describe()
     for b in bodies:
         b.OnDisable()
+    del bodies, copy_streams
+    t_ms, t_q, t_h, t_r, t_d2h = reduce_max([ms, q_ms, h_ms, r_ms, d2h_ms])
+
+    # ---- BASELINE config 5 at this GPU count: 4096 randomised ocean states x 3 cascades x 512^2 (noise -> spectrum ->
+    # one frame -> on-device checksums), sharded round robin over the ranks, no collective on the data path; the only
+    # communication is the final all_gather of the per-state checksums, whose digest must not depend on N. ----
+    ensemble = None
+    if not args.no_ensemble:
+        c5 = pkg.scene.config(5)
+        n_states = int(os.environ.get("OCEAN_BENCH_ENSEMBLE_STATES", str(c5["states"])))
+        batch = int(os.environ.get("OCEAN_BENCH_ENSEMBLE_BATCH", "16"))
+        oceans, seeds = pkg.scene.ensemble_states(n_states, c5["rng_seed"])
+        ens = pkg.OceanEnsemble(c5["N"], c5["cascades"], batch=batch, device=local)
+        mine = pkg.sharding.shard_indices(n_states, rank, world)
+        ens.run(oceans[mine][:2 * batch], seeds[mine][:2 * batch], time=c5["time"])  # warm-up: two waves, both lanes
+        barrier()
+        t0 = time.perf_counter()
+        local_sums = ens.run(oceans[mine], seeds[mine], time=c5["time"])  # synchronous: returns with the checksums on the host
+        torch.cuda.synchronize()
+        ens_s = time.perf_counter() - t0
+        barrier()
+        gather = pkg.sharding.torch_all_gather(device="cuda") if dist is not None else None
+        sums = pkg.sharding.run_sharded(lambda oc, sd: local_sums, oceans, seeds, rank, world, gather)
+        ens.close()
+        (ens_max,) = reduce_max([ens_s])
+        ensemble = {"metric": "ocean_instances_per_sec", "value": n_states / ens_max, "unit": "ocean-instances/s",
+                    "cascade_frames_per_sec": n_states * len(c5["cascades"]) / ens_max,
+                    "states": n_states, "batch": batch, "cascades": len(c5["cascades"]), "N": c5["N"], "scaling": "strong",
+                    "seconds": ens_max, "states_per_rank": int(len(mine)),
+                    "checksum_digest": hashlib.sha256(np.ascontiguousarray(sums).tobytes()).hexdigest()[:16],
+                    "what": "config 5: per state noise(seed) -> InitialSpectrum -> one frame at t = 1 s -> 64-bit checksums of the three "
+                            "output arrays; states sharded round robin (state s on rank s % N), host wall clock around "
+                            "ocean_ensemble_run incl. parameter upload and checksum download, max over ranks; digest = sha256 of the "
+                            "gathered [state][3] checksums (identical for every GPU count)"}
+
     if rank == 0:
         peak, peak_src = peaks()
         frame_bytes = ALG_BYTES_PER_TEXEL_CASCADE * N * N * C
         frame_ms = t_ms / K
         achieved = frame_bytes / (frame_ms * 1e-3) / 1e9
-        cpu = None
+        traffic, traffic_note = measured_traffic()
+        cpu = single = cfg1 = None
         if world == 1 and not args.no_cpu_baseline:
-            cpu = cpu_reference(steps=10 ** 6, warmup=1, max_seconds=12.0)
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
-            with open(tpath) as f:
-                traffic = json.load(f).get("frame_dram_bytes")
+            cpu = cpu_reference(steps=10 ** 6, warmup=1, max_seconds=10.0)
+            single = cpu_reference(steps=3, warmup=0, max_seconds=8.0, threads=1)
+            cfg1 = cpu_config1()
+        d2h_gbs = world * reps * N * N * 4 / (t_d2h * 1e-3) / 1e9
+        plane_gbs = world * K * N * N * 4 / (t_h * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": world * K * C / (t_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sharding": "independent ocean instances per GPU, no collective on the data path",
-                       "l2": "timed loop rotates over %d ocean instances on one stream (%.0f MB of inputs+outputs > 126 MB L2; "
-                             "the 33.5 MB row->column workspace is shared per stream and stays in L2)" % (
-                           INSTANCES, INSTANCES * (16 + 8 + 48) * N * N * C / 1e6),
-                       "kernels": describe},
-            "e2e": {"value": world * K * C / t_e2e, "unit": UNIT, "h2d_bytes_per_step": 4,
-                    "d2h_bytes_per_step": N * N * 4, "ms_per_step": 1e3 * t_e2e / K,
-                    "what": "ocean_update through the C ABI, host wall clock: frame + async readback to pinned host memory of the "
-                            "height channel of displacement layer 0 (what GetWaterHeight WB:195-209 reads; WaterBody.Update "
-                            "WB:284-297; the column pass writes the plane, the copy stream is released by the layer-0 column "
-                            "counter); the only per-step host input is the time scalar",
-                    "rgba_readback": {"value": world * K * C / t_e2e_rgba, "ms_per_step": 1e3 * t_e2e_rgba / K,
-                                      "d2h_bytes_per_step": N * N * 16,
+            "warmup": W, "prime": prime, "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": CONFIG, "kernels": describe,
+            "timing": "CUDA events on the launching stream; W warm-up frames, sync + barrier, then `prime` untimed frames issued "
+                      "back to back with the K timed ones (no sync in between) so that the K frames are steady-state pipelined frames",
+            "e2e": {"value": world * K * C / (t_q * 1e-3), "unit": UNIT, "ms_per_step": t_q / K,
+                    "h2d_bytes_per_step": BOXES * 24 + 4, "d2h_bytes_per_step": BOXES * 16,
+                    "host_wall_ms_per_step": q_wall / K, "answers_checksum": q_check,
+                    "what": "ocean_update_buoyancy through the C ABI: one frame, then BuoyantObject.FixedUpdate (BO:18-30) over "
+                            "WaterBody.GetWaterHeight (WB:195-209) for %d boxes answered on the owning GPU from the frame's height plane; "
+                            "boxes come from pinned host memory and answers return to it every step, on the handle's copy stream, released "
+                            "by the layer-0 column counter; device-timed from the compute stream's start event to the latest of the "
+                            "compute and copy streams; host_wall = the same K steps + final sync by the host clock" % BOXES,
+                    "plane_readback": {"value": world * K * C / (t_h * 1e-3), "ms_per_step": t_h / K, "d2h_bytes_per_step": N * N * 4,
+                                       "host_wall_ms_per_step": h_wall / K,
+                                       "d2h_GBps": plane_gbs, "d2h_ceiling_GBps": d2h_gbs, "frac_of_d2h_ceiling": plane_gbs / d2h_gbs,
+                                       "what": "the drop-in shape: ocean_update = frame + async readback to pinned host memory of the height "
+                                               "channel of displacement layer 0 (what GetWaterHeight reads, WB:206-208); ceiling = plain "
+                                               "cudaMemcpyAsync of 1 MiB blocks, one copy per block, from all %d rank(s) at once" % world},
+                    "rgba_readback": {"value": world * K * C / (t_r * 1e-3), "ms_per_step": t_r / K, "d2h_bytes_per_step": N * N * 16,
+                                      "host_wall_ms_per_step": r_wall / K,
                                       "what": "same with the reference's whole-layer RGBA32F request (WB:288), PCIe-bound"}},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "frac_of_nominal_8000": achieved / 8000.0,
+                         "traffic": traffic, "traffic_note": traffic_note, "peak_source": peak_src,
+                         "frac_of_nominal_8000": achieved / 8000.0,
                          "kernel": "frame = ocean_rows_kernel<512> + ocean_cols_tma_kernel<512> (two launches, overlapped by PDL; one launch = one frame)",
                          "algorithmic_bytes_per_launch": frame_bytes,
+                         "as_built_bytes_per_launch": BUILT_BYTES_PER_TEXEL_CASCADE * N * N * C,
+                         "as_built_frac": BUILT_BYTES_PER_TEXEL_CASCADE * N * N * C / (frame_ms * 1e-3) / 1e9 / peak,
                          "rows_ms": rows_ms, "cols_ms": cols_ms,
                          "rows_GBps_32B_per_texel": 32 * N * N * C / (rows_ms * 1e-3) / 1e9,
                          "cols_GBps_64B_per_texel": 64 * N * N * C / (cols_ms * 1e-3) / 1e9},
         }
+        if ensemble is not None:
+            line["ensemble"] = ensemble
         if cpu is not None:
             line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"]["single_thread"] = {k: single[k] for k in ("value", "unit", "cores", "sample")}
+            line["cpu_baseline"]["config1"] = cfg1
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
@@ -267,13 +459,14 @@ def run_cuda(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4000)
+    ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ensemble", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
-        if args.steps == 4000:
+        if args.steps == 2000:
             args.steps = 20
         run_reference(args)
     else:

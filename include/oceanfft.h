@@ -204,6 +204,18 @@ typedef struct OceanBuoyantBox {
 int ocean_buoyancy(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode /*OceanQueryMode*/, float density,
                    float gravityY, float* out4, int boxesOnDevice, int outOnDevice);
 
+/* WaterBody.Update (WB:284-297) + BuoyantObject.FixedUpdate (BO:18-30) with the queries answered on the owning GPU:
+ * one frame at `time`, then -- on the handle's copy stream, released as soon as the columns of layer 0 are done -- the n
+ * boxes are copied to the device, looked up in that frame's height plane exactly as OCEAN_QUERY_NEAREST_REF does
+ * (WB:195-209) and run through BO:19-29; out4 receives n x (waterHeight, heightSubmerged, acceleration, submergedVolume).
+ * Instead of the reference's N*N*16 B layer per frame, 24 B per box travel in and 16 B per box travel out.
+ * Fully asynchronous: `boxes` and `out4` are host buffers (pinned for real overlap) that must stay untouched until
+ * ocean_sync(h) -- or until three later ocean_update / ocean_update_buoyancy calls on h have been issued, the depth of
+ * the readback ring.  The frame's layer is NOT shipped: OCEAN_QUERY_READBACK_REF keeps answering from the last
+ * ocean_update. */
+int ocean_update_buoyancy(OceanHandle* h, float time, const OceanBuoyantBox* boxes, int n, float density, float gravityY,
+                          float* out4);
+
 /* ---- foam state: the persistence implicit in the turbulence RenderTexture RF:28,32 --------- */
 int ocean_set_turbulence(OceanHandle* h, const float* host /* C*N*N*4 */);
 int ocean_reset_foam(OceanHandle* h);
@@ -218,6 +230,8 @@ int ocean_query_heights(OceanHandle* h, const float* worldXZ, int n, int mode /*
 /* ---- plumbing ------------------------------------------------------------------------------ */
 int ocean_get_stream(OceanHandle* h, void** cudaStream);
 int ocean_set_stream(OceanHandle* h, void* cudaStream); /* share one stream between handles (NULL = own) */
+/* The second stream of the handle (cudaStream_t as void*): readbacks and ocean_update_buoyancy answers complete on it. */
+int ocean_get_copy_stream(OceanHandle* h, void** cudaStream);
 /* Kernel launches issued by this library on the calling thread's behalf since load (bench bookkeeping). */
 uint64_t ocean_launch_count(void);
 /* Names of the most recent launch configuration, for DESIGN.md / bench: writes a short text. */

@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "ocean_ensemble_create", "ocean_ensemble_destroy", "ocean_ensemble_run",
     "ocean_ensemble_get_output", "ocean_ensemble_copy_output",
     "ocean_generate_mips", "ocean_set_auto_mips", "ocean_mip_levels", "ocean_get_mips", "ocean_copy_mip",
-    "ocean_sample_surface", "ocean_buoyancy",
+    "ocean_sample_surface", "ocean_buoyancy", "ocean_update_buoyancy", "ocean_get_copy_stream",
 ]
 
 
@@ -112,6 +112,8 @@ def load():
     L.ocean_copy_mip.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, fp]
     L.ocean_sample_surface.argtypes = [vp, vp, ctypes.c_int, ctypes.c_float, vp, vp, vp, ctypes.c_int]
     L.ocean_buoyancy.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp, ctypes.c_int, ctypes.c_int]
+    L.ocean_update_buoyancy.argtypes = [vp, ctypes.c_float, vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp]
+    L.ocean_get_copy_stream.argtypes = [vp, ctypes.POINTER(vp)]
     _lib = L
     return L
 

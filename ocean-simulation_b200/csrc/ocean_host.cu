@@ -320,6 +320,12 @@ struct OceanHandle {
     int rbSlotMode[RB] = {0, 0, 0};               // layout of each slot's host copy
     bool rbPending[RB] = {false, false, false};
     int rbLatest = -1;  // slot of the newest completed readback
+    // ocean_update_buoyancy: the slot's staging plane is consumed on the device (boxes in, answers out); no plane
+    // reaches the host, so such a slot never becomes the visible buoyancyData
+    bool rbHasPlane[RB] = {true, true, true};
+    OceanBuoyantBox* rbBoxes[RB] = {nullptr, nullptr, nullptr};
+    float4* rbAnswers[RB] = {nullptr, nullptr, nullptr};
+    int rbBoxCap[RB] = {0, 0, 0};
     // HEIGHT mode: the column pass itself writes the height plane of layer 0 into the slot's staging buffer;
     // the copy stream waits (stream memory operation) for the layer-0 column counter and ships it -- the
     // compute stream carries nothing but the two frame kernels
@@ -348,6 +354,8 @@ struct OceanHandle {
     int CalculateInitialSpectrumTextures();
     int CalculateWavesTexturesAtTime(float time, int which = 0, float* heightOut = nullptr);
     int Update(float time);
+    int UpdateBuoyancy(float time, const OceanBuoyantBox* boxes, int n, float density, float gravityY, float* out4);
+    int PickSlot(int* slot);
     void PollReadbacks(bool wait);
     int GetWaterHeight(const float* worldXZ, int n, int mode, float* heights, bool ptsDev, bool outDev);
     int AttachWorkspace(cudaStream_t shared);
@@ -562,7 +570,7 @@ void OceanHandle::PollReadbacks(bool wait) {
         if (!rbPending[i]) continue;
         if (SlotDone(i, wait)) {
             rbPending[i] = false;
-            if (rbLatest < 0 || rbFrame[i] > rbFrame[rbLatest]) rbLatest = i;
+            if (rbHasPlane[i] && (rbLatest < 0 || rbFrame[i] > rbFrame[rbLatest])) rbLatest = i;
         }
     }
 }
@@ -577,27 +585,74 @@ extern "C" void ocean_debug_host_prof() { for (int i = 0; i < 8; ++i) printf("pr
 #else
 #define PROF(k)
 #endif
+// A readback slot that is neither in flight nor the visible buoyancyData; blocks on the oldest request if none is free.
+int OceanHandle::PickSlot(int* slot) {
+    int s = -1;
+    for (;;) {
+        PollReadbacks(false);
+        for (int i = 0; i < RB && s < 0; ++i)
+            if (!rbPending[i] && i != rbLatest) s = i;
+        if (s >= 0) break;
+        int oldest = -1;
+        for (int i = 0; i < RB; ++i)
+            if (rbPending[i] && (oldest < 0 || rbFrame[i] < rbFrame[oldest])) oldest = i;
+        if (!SlotDone(oldest, true)) return fail(OCEAN_ERR_CUDA, "readback of frame %lld did not complete", (long long)rbFrame[oldest]);
+    }
+    *slot = s;
+    return OCEAN_OK;
+}
+
+// One frame + BuoyantObject.FixedUpdate (BO:18-30) for n boxes answered ON THE OWNING GPU: WaterBody.Update ships layer 0
+// to the host every frame so that FixedUpdate can look heights up there (WB:288-296, BO:18); here the boxes travel to the
+// device (24 B each), the lookup + force arithmetic runs against the frame's height plane, and 16 B per box travel back.
+// Everything but the frame itself is on the copy stream, released by the layer-0 column counter like the HEIGHT readback,
+// so the compute stream still carries nothing but the two frame kernels.
+int OceanHandle::UpdateBuoyancy(float time, const OceanBuoyantBox* boxes, int n, float density, float gravityY, float* out4) {
+    if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_update_buoyancy before ocean_init_spectrum");
+    int s = -1;
+    { int rc = PickSlot(&s); if (rc != OCEAN_OK) return rc; }
+    if (n > rbBoxCap[s]) {
+        if (rbBoxes[s]) cudaFree(rbBoxes[s]);
+        if (rbAnswers[s]) cudaFree(rbAnswers[s]);
+        rbBoxes[s] = nullptr; rbAnswers[s] = nullptr; rbBoxCap[s] = 0;
+        OCEAN_CUDA(cudaMalloc(&rbBoxes[s], (size_t)n * sizeof(OceanBuoyantBox)));
+        OCEAN_CUDA(cudaMalloc(&rbAnswers[s], (size_t)n * sizeof(float4)));
+        rbBoxCap[s] = n;
+    }
+    float* plane = (float*)rbStage[s];
+    if (n > 0) OCEAN_CUDA(cudaMemcpyAsync(rbBoxes[s], boxes, (size_t)n * sizeof(OceanBuoyantBox), cudaMemcpyHostToDevice, copyStream));
+    if (stream_wait_value_available()) {
+        int rc = CalculateWavesTexturesAtTime(time, 0, plane);
+        if (rc != OCEAN_OK) return rc;
+        const unsigned long long* colsDone0 = ws->counters + ws->layers;  // layer 0 of this ocean
+        OCEAN_CUDA(stream_wait_value_geq(copyStream, colsDone0, (unsigned long long)N * ws->colPasses));
+    } else {
+        int rc = CalculateWavesTexturesAtTime(time);
+        if (rc != OCEAN_OK) return rc;
+        OCEAN_CUDA(launch_pack_height(disp, plane, (int)texels(), stream));
+        OCEAN_CUDA(cudaEventRecord(rbSnap, stream));
+        OCEAN_CUDA(cudaStreamWaitEvent(copyStream, rbSnap, 0));
+    }
+    if (n > 0) {
+        OCEAN_CUDA(launch_buoyancy_plane(rbBoxes[s], plane, N, n, density, gravityY, rbAnswers[s], copyStream));
+        OCEAN_CUDA(cudaMemcpyAsync(out4, rbAnswers[s], (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, copyStream));
+    }
+    OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
+    rbSlotMode[s] = OCEAN_READBACK_HEIGHT;
+    rbHasPlane[s] = false;
+    rbFrame[s] = frame - 1;
+    rbPending[s] = true;
+    return OCEAN_OK;
+}
+
 int OceanHandle::Update(float time) {
 #ifdef OCEAN_HOST_PROF
     ++g_profN;
 #endif
     PROF(0);
     if (!spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_update before ocean_init_spectrum");
-    // pick a slot that is neither in flight nor the visible buoyancyData
     int s = -1;
-    {
-        PROF(2);
-        for (;;) {
-            PollReadbacks(false);
-            for (int i = 0; i < RB && s < 0; ++i)
-                if (!rbPending[i] && i != rbLatest) s = i;
-            if (s >= 0) break;
-            int oldest = -1;
-            for (int i = 0; i < RB; ++i)
-                if (rbPending[i] && (oldest < 0 || rbFrame[i] < rbFrame[oldest])) oldest = i;
-            if (!SlotDone(oldest, true)) return fail(OCEAN_ERR_CUDA, "readback of frame %lld did not complete", (long long)rbFrame[oldest]);
-        }
-    }
+    { PROF(2); int rc = PickSlot(&s); if (rc != OCEAN_OK) return rc; }
     if (rbMode == OCEAN_READBACK_HEIGHT && stream_wait_value_available()) {
         // Only the channel GetWaterHeight reads (WB:206-208): the column pass writes it into the slot's staging
         // plane; the copy stream starts as soon as the columns of layer 0 are done.
@@ -625,6 +680,7 @@ int OceanHandle::Update(float time) {
         OCEAN_CUDA(cudaEventRecord(rbDone[s], copyStream));
     }
     rbSlotMode[s] = rbMode;
+    rbHasPlane[s] = true;
     rbFrame[s] = frame - 1;
     rbPending[s] = true;
     return OCEAN_OK;
@@ -687,7 +743,8 @@ void OceanHandle::OnDisable() {
     if (copyStream) cudaStreamSynchronize(copyStream);
     workspace_release(ws);
     ws = nullptr;
-    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, bBuf, auxDone};
+    void* dev[] = {noise, h0, wave, waveHot, h0c, disp, deriv, turb, twiddle, stateDev, seedDev, rbStage[0], rbStage[1], rbStage[2], qPts, qOut, derivMips, turbMips, sBuf, bBuf, auxDone,
+                   rbBoxes[0], rbBoxes[1], rbBoxes[2], rbAnswers[0], rbAnswers[1], rbAnswers[2]};
     for (void* p : dev)
         if (p) cudaFree(p);
     for (int i = 0; i < RB; ++i) {
@@ -970,6 +1027,13 @@ int ocean_update(OceanHandle* h, float time) {
     return h->Update(time);
 }
 
+int ocean_update_buoyancy(OceanHandle* h, float time, const OceanBuoyantBox* boxes, int n, float density, float gravityY, float* out4) {
+    if (!h || (n > 0 && (!boxes || !out4))) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
+    DeviceScope scope(h->device);
+    return h->UpdateBuoyancy(time, boxes, n, density, gravityY, out4);
+}
+
 int ocean_sync(OceanHandle* h) {
     if (!h) return fail(OCEAN_ERR_INVALID_ARGUMENT, "handle is NULL");
     DeviceScope scope(h->device);
@@ -1161,6 +1225,12 @@ int ocean_sample_surface(OceanHandle* h, const float* worldXZ, int n, float lod,
 int ocean_get_stream(OceanHandle* h, void** s) {
     if (!h || !s) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
     *s = (void*)h->stream;
+    return OCEAN_OK;
+}
+
+int ocean_get_copy_stream(OceanHandle* h, void** s) {
+    if (!h || !s) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    *s = (void*)h->copyStream;
     return OCEAN_OK;
 }
 

@@ -146,6 +146,9 @@ cudaError_t launch_displaced_query(const float4* disp, int N, int C, const float
 cudaError_t launch_buoyancy_points(const OceanBuoyantBox* boxes, float2* pts, int n, cudaStream_t s);
 cudaError_t launch_buoyancy(const OceanBuoyantBox* boxes, const float* heights, int n, float density, float gravityY, float4* out,
                             cudaStream_t s);
+// BO:18-30 over WB:195-209 on a frame's height plane (N*N floats, the .g channel of displacement layer 0), one launch
+cudaError_t launch_buoyancy_plane(const OceanBuoyantBox* boxes, const float* plane, int N, int n, float density, float gravityY,
+                                  float4* out, cudaStream_t s);
 cudaError_t launch_pack_height(const float4* dispLayer, float* out, int n, cudaStream_t s);
 cudaError_t launch_checksum(const float4* arr, int nStates, size_t float4PerState, unsigned long long* out /*[state]*/,
                             int outStride, cudaStream_t s);

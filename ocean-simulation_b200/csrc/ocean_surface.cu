@@ -277,6 +277,41 @@ __global__ void ocean_buoyancy_kernel(const OceanBuoyantBox* __restrict__ boxes,
     }
     out[i] = make_float4(waterHeight, heightSubmerged, accel, volume);
 }
+// The whole of BuoyantObject.FixedUpdate BO:18-30 over WaterBody.GetWaterHeight WB:195-209 in one launch, reading the
+// HEIGHT PLANE of a frame (the .g channel of displacement layer 0 that the column pass writes for the readback,
+// FrameArgs::heightOut) instead of the RGBA layer: what ocean_update_buoyancy runs on the owning GPU so that only the
+// boxes and their answers cross PCIe.  Same fp32 operations as ocean_query_kernel (NEAREST_REF) + ocean_buoyancy_kernel.
+__global__ void ocean_buoyancy_plane_kernel(const OceanBuoyantBox* __restrict__ boxes, const float* __restrict__ plane, int N, int n,
+                                            float density, float absGravityY, float4* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const OceanBuoyantBox b = boxes[i];
+    // Mathf.InverseLerp(-N/2, N/2, v) = Clamp01((v - a) / (b - a))   WB:199-200
+    const float lo = (float)(-(N / 2)), hi = (float)(N / 2);
+    float u = __fdiv_rn(__fsub_rn(b.px, lo), __fsub_rn(hi, lo));
+    float v = __fdiv_rn(__fsub_rn(b.pz, lo), __fsub_rn(hi, lo));
+    u = fminf(fmaxf(u, 0.0f), 1.0f);
+    v = fminf(fmaxf(v, 0.0f), 1.0f);
+    int x = (int)__fmul_rn(u, (float)N), y = (int)__fmul_rn(v, (float)N);  // WB:203-204
+    x = min(max(x, 0), N - 1);
+    y = min(max(y, 0), N - 1);
+    const float waterHeight = __ldcg(&plane[(size_t)y * N + x]);            // .g of layer 0  WB:206-208, BO:18
+    const float heightSubmerged = fmaxf(0.0f, waterHeight - b.py);         // BO:19
+    float volume = 0.0f, accel = 0.0f;
+    if (heightSubmerged > 0.0f) {                                           // BO:21
+        const float fullVolume = b.sx * b.sy * b.sz;                        // BO:24
+        volume = fminf(fmaxf(heightSubmerged / b.sy, 0.0f), 1.0f) * fullVolume;  // BO:25
+        const float buoyantForce = density * volume;                        // BO:26
+        accel = absGravityY * buoyantForce;                                 // BO:29
+    }
+    out[i] = make_float4(waterHeight, heightSubmerged, accel, volume);
+}
+cudaError_t launch_buoyancy_plane(const OceanBuoyantBox* boxes, const float* plane, int N, int n, float density, float gravityY,
+                                  float4* out, cudaStream_t s) {
+    ocean_buoyancy_plane_kernel<<<(n + 127) / 128, 128, 0, s>>>(boxes, plane, N, n, density, fabsf(gravityY), out);
+    count_launch();
+    return cudaGetLastError();
+}
 cudaError_t launch_buoyancy_points(const OceanBuoyantBox* boxes, float2* pts, int n, cudaStream_t s) {
     ocean_buoyancy_points_kernel<<<(n + 255) / 256, 256, 0, s>>>(boxes, pts, n);
     count_launch();

@@ -200,6 +200,24 @@ class WaterBody:
                                          out.ctypes.data, 0, 0))
         return out
 
+    def UpdateBuoyancy(self, time, boxes, out, density=1.0, gravityY=-9.81):
+        """WaterBody.Update + BuoyantObject.FixedUpdate with the lookups answered on the owning GPU (ocean_update_buoyancy).
+        boxes: float32 [n][6] and out: float32 [n][4], caller-owned (pinned for overlap) and untouched until Sync().
+        Pass numpy arrays or (data_ptr, n) pairs of pinned torch tensors."""
+        if isinstance(boxes, tuple):
+            bptr, n = boxes
+            optr = out[0] if isinstance(out, tuple) else out.ctypes.data
+        else:
+            assert boxes.dtype == np.float32 and boxes.flags.c_contiguous and out.dtype == np.float32 and out.flags.c_contiguous
+            bptr, n, optr = boxes.ctypes.data, boxes.shape[0], out.ctypes.data
+        L.check(self._lib.ocean_update_buoyancy(self._need(), float(time), bptr, int(n), float(density), float(gravityY), optr))
+
+    @property
+    def copyStream(self):
+        s = ctypes.c_void_p()
+        L.check(self._lib.ocean_get_copy_stream(self._need(), ctypes.byref(s)))
+        return s.value
+
     def SetReadbackMode(self, mode):
         """L.READBACK_RGBA (the reference's whole-layer request, default) or L.READBACK_HEIGHT (packed .g only)."""
         L.check(self._lib.ocean_set_readback_mode(self._need(), int(mode)))

@@ -35,7 +35,8 @@ static const void* const kSymbols[] = {
     (const void*)ocean_reset_foam, (const void*)ocean_frame_index, (const void*)ocean_query_heights,
     (const void*)ocean_get_stream, (const void*)ocean_set_stream, (const void*)ocean_launch_count, (const void*)ocean_describe,
     (const void*)ocean_ensemble_create, (const void*)ocean_ensemble_destroy, (const void*)ocean_ensemble_run,
-    (const void*)ocean_ensemble_get_output, (const void*)ocean_ensemble_copy_output,
+    (const void*)ocean_ensemble_get_output, (const void*)ocean_ensemble_copy_output, (const void*)ocean_update_buoyancy,
+    (const void*)ocean_get_copy_stream,
 };
 
 static const OceanCascade kCascades[2] = {{1530.0f, 1e-10f, 1e12f, 0.4f, 0.1f}, {201.0f, 1e-5f, 1e6f, 0.1f, 0.1f}};
@@ -106,6 +107,14 @@ static int device_flow(void) {
     EXPECT(rb != NULL && frame == 3);
     EXPECT(ocean_copy_output(h, OCEAN_DISPLACEMENT, 0, disp) == OCEAN_OK);
     EXPECT(memcmp(rb, disp, sizeof(float) * N * N * 4) == 0);
+    /* the same answer from the owning GPU, one frame later at the same time (same displacement) */
+    EXPECT(ocean_update_buoyancy(h, 0.1f, &box, 1, 1.0f, -9.81f, out4) == OCEAN_OK);
+    EXPECT(ocean_sync(h) == OCEAN_OK);
+    {
+        float again[4];
+        EXPECT(ocean_buoyancy(h, &box, 1, OCEAN_QUERY_NEAREST_REF, 1.0f, -9.81f, again, 0, 0) == OCEAN_OK);
+        EXPECT(memcmp(again, out4, sizeof again) == 0);
+    }
     EXPECT(ocean_describe(h, text, sizeof text) == OCEAN_OK && strstr(text, "N=64") != NULL);
     ocean_destroy(h);
     free(disp);

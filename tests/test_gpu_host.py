@@ -116,3 +116,45 @@ def test_ensemble_rejects_a_wave_with_mixed_lambda(pkg, po):
     assert mixed[:2].tolist() == ones[:2].tolist() and mixed[2:].tolist() == halves[2:].tolist()
     assert mixed[2:].tolist() != ones[2:].tolist()
     ens.close()
+
+
+@pytest.mark.parametrize("N", [128, 256, 512])  # plain-load columns, fused frame kernel, TMA columns
+def test_update_buoyancy_answers_on_the_owning_gpu(pkg, po, N):
+    """ocean_update_buoyancy: frame + BO:18-30 over WB:195-209 against the frame's height plane on the copy stream.
+    Eight pipelined frames with a ring of host buffers must equal, bit for bit, a twin ocean stepped synchronously
+    and asked through ocean_buoyancy(NEAREST_REF); READBACK_REF keeps serving the last shipped layer."""
+    cfg = pkg.scene.config(2)
+    body, noise = make_body(pkg, po, cfg, N=N)
+    twin, _ = make_body(pkg, po, cfg, N=N, noise=noise)
+    rng = np.random.default_rng(77)
+    n = 4096
+    boxes = np.empty((n, 6), np.float32)
+    boxes[:, 0] = rng.uniform(-N / 2 - 5, N / 2 + 5, n)
+    boxes[:, 2] = rng.uniform(-N / 2 - 5, N / 2 + 5, n)
+    boxes[:, 1] = rng.uniform(-2, 2, n)
+    boxes[:, 3:] = rng.uniform(0.2, 3.0, (n, 3))
+    body.Update(0.0)
+    twin.CalculateWavesTexturesAtTime(0.0)
+    frame0, layer0 = body.WaitReadback()
+    ring = [np.full((n, 4), np.nan, np.float32) for _ in range(3)]
+    ins = [boxes.copy() for _ in range(3)]
+    want = []
+    for f in range(1, 9):
+        k = f % 3
+        if f > 3:  # the slot's previous answer (frame f - 3) is complete by the contract: check it before reuse
+            body.Sync()
+            assert np.array_equal(ring[k], want[f - 4]), "frame %d" % (f - 3)
+        ins[k][:, 1] = boxes[:, 1] + np.float32(0.01 * f)
+        body.UpdateBuoyancy(f / 60.0, ins[k], ring[k], density=0.9, gravityY=-9.81)
+        twin.CalculateWavesTexturesAtTime(f / 60.0)
+        want.append(twin.Buoyancy(ins[k], pkg._lib.QUERY_NEAREST_REF, density=0.9, gravityY=-9.81))
+    body.Sync()
+    for f in (6, 7, 8):
+        assert np.array_equal(ring[f % 3], want[f - 1])
+    assert (want[-1][:, 1] > 0).sum() > 100 and (want[-1][:, 1] == 0).sum() > 100
+    assert np.array_equal(body.displacementsTextures, twin.displacementsTextures)
+    # no layer was shipped since frame 0: the reference-latency lookup still answers from it
+    frame, layer = body.WaitReadback()
+    assert frame == frame0 and np.array_equal(layer, layer0)
+    body.OnDisable()
+    twin.OnDisable()
