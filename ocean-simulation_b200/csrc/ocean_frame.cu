@@ -883,6 +883,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 }
 
 #include "ocean_fused.cuh"
+#include "ocean_fused2.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // WaterBody.GetWaterHeight WB:195-209 (mode 0), plus bilinear extensions at the shader's own
@@ -1075,24 +1076,57 @@ template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsT
     const int grid = totalItems < slots ? totalItems : slots;
     return launch_pdl(early, a, ocean_frame_kernel<N>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a);
 }
+template <int N> static int frame2_ctas_per_sm() {
+    using Cfg = Fused2Cfg<N>;
+    static int ctasPerSM = 0;
+    if (ctasPerSM == 0) {
+        cudaFuncSetAttribute(ocean_frame2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        cudaFuncSetAttribute(ocean_frame2_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_frame2_kernel<N>, Cfg::THREADS, Cfg::SMEM_BYTES);
+        ctasPerSM = n > 0 ? n : 1;
+    }
+    return ctasPerSM;
+}
+template <int N> static int frame2_grid(int layers) {
+    const int totalItems = 2 * layers * Fused2Cfg<N>::IPL;
+    const int slots = num_sms() * frame2_ctas_per_sm<N>();
+    return totalItems < slots ? totalItems : slots;
+}
+template <int N> static cudaError_t frame2_launch(const FrameArgs& a, const ColsTmaMaps& m, cudaStream_t s, bool early) {
+    using Cfg = Fused2Cfg<N>;
+    return launch_pdl(early, a, ocean_frame2_kernel<N>, dim3(frame2_grid<N>(a.layers)), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a);
+}
 static bool tma_size(int N) { return N == 256 || N == 512 || N == 1024; }
-// The whole frame as one persistent kernel.  Default at N = 256, where the frame is a latency chain and one
-// launch beats two (config 1: 9.3 vs 10.5 us, config 2: 10.0 vs 13.0 us).  At N = 512 the two-kernel path
-// wins (26.5 vs 29.4 us at 4 x 512^2: the fused kernel's items still wait for their just-in-time loads, see
-// DESIGN.md).  OCEAN_FUSED=0 / 1 (or -DOCEAN_USE_FUSED) forces it off / on for both sizes.
-bool frame_fused_available(int N, const ColsTmaMaps* maps) {
-    if (!(N == 256 || N == 512) || !maps || !maps->valid) return false;
-#ifdef OCEAN_USE_FUSED
-    return true;
-#else
+// The whole frame as one persistent kernel.  Mode 1 (static round robin) was the default at N = 256 in round 1, where the
+// frame is a latency chain and one launch beats two (config 1: 9.3 vs 10.5 us, config 2: 10.0 vs 13.0 us); at N = 512 it
+// lost to the two-kernel path (29.4 vs 26.5 us at 4 x 512^2: its items waited for their loads and for each other).  Mode 2
+// (ocean_fused2.cuh) hands items out dynamically and prefetches.  OCEAN_FUSED=0 / 1 / 2 forces a mode for both sizes.
+#ifndef OCEAN_FUSED_DEFAULT_256
+#define OCEAN_FUSED_DEFAULT_256 1
+#endif
+#ifndef OCEAN_FUSED_DEFAULT_512
+#define OCEAN_FUSED_DEFAULT_512 0
+#endif
+int frame_fused_mode(int N, const ColsTmaMaps* maps) {
+    if (!(N == 256 || N == 512) || !maps || !maps->valid) return 0;
     static const int mode = [] {
         const char* e = getenv("OCEAN_FUSED");
-        return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1);
+        return e == nullptr ? -1 : (e[0] - '0');
     }();
-    return mode < 0 ? N == 256 : mode == 1;
-#endif
+    if (mode >= 0 && mode <= 2) return mode;
+    return N == 256 ? OCEAN_FUSED_DEFAULT_256 : OCEAN_FUSED_DEFAULT_512;
 }
-cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early) {
+int frame_fused_grid(int N, int layers, int mode) {
+    if (mode != 2) return 0;
+    return N == 512 ? frame2_grid<512>(layers) : frame2_grid<256>(layers);
+}
+cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early, int mode) {
+    if (mode == 2) {
+        if (a.N == 512) return frame2_launch<512>(a, *maps, s, early);
+        if (a.N == 256) return frame2_launch<256>(a, *maps, s, early);
+        return cudaErrorNotSupported;
+    }
     if (a.N == 512) return frame_launch<512>(a, *maps, s, early);
     if (a.N == 256) return frame_launch<256>(a, *maps, s, early);
     return cudaErrorNotSupported;

@@ -164,9 +164,12 @@ struct Workspace {
     // planes (row -> column), counters[layers..2*layers) = columns consumed and stored (column -> row).
     // rowPasses / colPasses count the passes ENQUEUED on this workspace (its users are serialised by
     // one stream, so enqueue order is execution order); a pass's target is N * its ordinal.
+    // counters[2*layers + {0, 1}] = the item queues of the dynamically scheduled frame kernel (ocean_fused2.cuh), used
+    // alternately by consecutive frames; queueUses[i] * (items + grid) is where queue i's next frame starts.
     int layers = 0;
     unsigned long long* counters = nullptr;
     uint64_t rowPasses = 0, colPasses = 0;
+    uint64_t queueFrames = 0, queueNext[2] = {0, 0};
     float4* planeA() const { return base; }
     float4* planeB() const { return (float4*)((char*)base + planeBytes); }
 };
@@ -183,8 +186,8 @@ static Workspace* workspace_acquire(int device, cudaStream_t shared, int N, int 
     w->device = device; w->stream = shared; w->planeBytes = planeBytes; w->refs = 1;
     w->N = N; w->layers = layers;
     if (cudaMalloc(&w->base, 2 * planeBytes) != cudaSuccess) { delete w; return nullptr; }
-    if (cudaMalloc(&w->counters, 2 * layers * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMemset(w->counters, 0, 2 * layers * sizeof(unsigned long long)) != cudaSuccess) {
+    if (cudaMalloc(&w->counters, (2 * layers + 2) * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(w->counters, 0, (2 * layers + 2) * sizeof(unsigned long long)) != cudaSuccess) {
         cudaFree(w->base);
         delete w;
         return nullptr;
@@ -203,6 +206,13 @@ static void workspace_release(Workspace* w) {
     delete w;
 }
 // Stamps a frame's hand-off targets.  rows / cols say which passes this launch sequence contains.
+// Assigns the frame an item queue (fused frame kernel, dynamic scheduling): totalItems + grid fetches will be made.
+static void workspace_stamp_queue(Workspace* w, int totalItems, int grid, FrameArgs* a) {
+    const int q = (int)(w->queueFrames++ & 1);
+    a->itemNext = w->counters + 2 * w->layers + q;
+    a->itemBase = w->queueNext[q];
+    w->queueNext[q] += (uint64_t)totalItems + (uint64_t)grid;
+}
 static void workspace_stamp(Workspace* w, int N, bool rows, bool cols, FrameArgs* a) {
     if (rows) ++w->rowPasses;
     a->rowsDone = w->counters;
@@ -453,8 +463,11 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which, float* heig
     a.auxDone = auxSignals ? auxDone : nullptr;  // only once a reader has been launched on this ocean
     a.auxTarget = auxSignals;
     a.heightOut = heightOut;
-    if (which == 0 && !auxSignals && frame_fused_available(N, &colsMaps)) {
-        OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true));
+    a.gravity = params.gravity;
+    const int fusedMode = which == 0 && !auxSignals ? frame_fused_mode(N, &colsMaps) : 0;
+    if (fusedMode) {
+        if (fusedMode == 2) workspace_stamp_queue(ws, 2 * C * (N / 4), frame_fused_grid(N, C, 2), &a);
+        OCEAN_CUDA(launch_frame(a, &colsMaps, stream, true, fusedMode));
         foamZero = false;
         ++frame;
         return autoMips ? GenerateMips() : OCEAN_OK;
@@ -887,15 +900,20 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         fa.zeroFoam = 1;
         // a short last wave leaves the upper layers' counters behind: restart the counting per wave
         L.ws->rowPasses = L.ws->colPasses = 0;
-        OCEAN_CUDA(cudaMemsetAsync(L.ws->counters, 0, (size_t)2 * L.ws->layers * sizeof(unsigned long long), stream));
+        L.ws->queueFrames = 0; L.ws->queueNext[0] = L.ws->queueNext[1] = 0;
+        OCEAN_CUDA(cudaMemsetAsync(L.ws->counters, 0, (size_t)(2 * L.ws->layers + 2) * sizeof(unsigned long long), stream));
         workspace_stamp(L.ws, N, true, true, &fa);
         l2_window(device, L.ws, &fa);
         if (fusedInit) {
             fa.checksums = L.sumDev;  // reduced inside the column pass: the outputs are not read back
             OCEAN_CUDA(launch_rows_from_noise(ia, fa, stream));
             OCEAN_CUDA(launch_cols(fa, &L.colsMaps, stream));
-        } else if (frame_fused_available(N, &L.colsMaps)) {
-            OCEAN_CUDA(launch_frame(fa, &L.colsMaps, stream, false));  // follows the init kernel: no early start
+        } else if (const int fusedMode = frame_fused_mode(N, &L.colsMaps)) {
+            if (fusedMode == 2) {
+                fa.states = L.stateDev;  // gravity per state
+                workspace_stamp_queue(L.ws, 2 * nb * C * (N / 4), frame_fused_grid(N, nb * C, 2), &fa);
+            }
+            OCEAN_CUDA(launch_frame(fa, &L.colsMaps, stream, false, fusedMode));  // follows the init kernel: no early start
             OCEAN_CUDA(launch_checksum(L.disp, nb, stateFloat4(), L.sumDev + 0, 3, stream));
             OCEAN_CUDA(launch_checksum(L.deriv, nb, stateFloat4(), L.sumDev + 1, 3, stream));
             OCEAN_CUDA(launch_checksum(L.turb, nb, stateFloat4(), L.sumDev + 2, 3, stream));

@@ -91,6 +91,16 @@ struct FrameArgs {
     // Ensembles: when not nullptr the column pass adds, per state (= layer / C), the 64-bit sums of the fp32
     // bit patterns of the texels it produces to checksums[state * 3 + {0: disp, 1: deriv, 2: turb}].
     unsigned long long* checksums;
+    // Item queue of the fused frame kernel with dynamic scheduling (ocean_fused2.cuh): every item of the frame is handed
+    // out by one atomicAdd on *itemNext; the frame's items are the values itemBase .. itemBase + totalItems - 1, and every
+    // CTA makes exactly one fetch beyond them, so the counter advances by totalItems + gridDim.x per frame.  Two counters
+    // alternate between consecutive frames (their kernels overlap one deep under PDL).
+    unsigned long long* itemNext;
+    unsigned long long itemBase;
+    // Gravity for omega = sqrt(g |k|) (IS:33-35), recomputed by that kernel instead of loading (1/|k|, omega): per state
+    // (= layer / C) when `states` is set (ensembles), else the scalar.
+    const StateConsts* states;
+    float gravity;
     // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
     // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
     const void* l2Window;
@@ -122,10 +132,12 @@ cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaS
 // legal when that kernel does not produce h0 / waveHot / twiddles (i.e. it is a column pass).
 cudaError_t launch_rows(const FrameArgs& a, cudaStream_t s, bool early);
 cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s);
-// The whole frame as one persistent kernel (ocean_fused.cuh), where available (N = 256, 512).
-bool frame_fused_available(int N, const ColsTmaMaps* maps);
+// The whole frame as one persistent kernel, where available (N = 256, 512): 0 = no (two kernels), 1 = static round robin
+// (ocean_fused.cuh), 2 = dynamic queue + prefetch (ocean_fused2.cuh).  OCEAN_FUSED=0/1/2 overrides the default.
+int frame_fused_mode(int N, const ColsTmaMaps* maps);
+int frame_fused_grid(int N, int layers, int mode);  // persistent grid size of that kernel (FrameArgs::itemBase arithmetic)
 bool rows_need_h0c();  // the selected row pass reads FrameArgs::h0c / InitArgs::h0c (else they stay nullptr)
-cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early);
+cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early, int mode);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);
 // ocean_surface.cu: mip chain (WB:191-192), surface shading inputs (Water.shader:322-347), displaced queries

@@ -21,6 +21,10 @@ VARIANTS = {
     "fast_sincos": ["-DOCEAN_ROWS_FAST_SINCOS=1"],
     "early_producer": ["-DOCEAN_COLS_EARLY_PRODUCER=1"],
     "rows_r2": ["-DOCEAN_ROWS512_R=2", "-DOCEAN_ROWS512_MINB=7"],
+    # fused2 timing experiments (OCEAN_F2_EXP bits, ocean_fused2.cuh)
+    "f2x1_fast_hot": ["-DOCEAN_F2_EXP=1"],
+    "f2x2_no_foam_load": ["-DOCEAN_F2_EXP=2"],
+    "f2x3_both": ["-DOCEAN_F2_EXP=3"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()
