@@ -174,7 +174,8 @@ __device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned
 #endif
 // Sensitivity experiments (variants/build_variants.py; results are WRONG, only the timing is of interest):
 // 1: row pass reads L2-resident rows, 2: column pass stores nothing, 4: no turbulence load, 8: row pass stores nothing,
-// 32: no sincos in the row pass, 64: both kernels only wait for / publish their counters (launch + hand-off floor), 128: both kernels return at once
+// 32: no sincos in the row pass, 64: both kernels only wait for / publish their counters (launch + hand-off floor), 128: both kernels return at once,
+// 256: the column pass does not wait for its rows (variants/deferred_probe.py)
 #ifndef OCEAN_EXP
 #define OCEAN_EXP 0
 #endif
@@ -749,7 +750,9 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         auto await_rows = [&](int tile) {
             const int layer = tile / TILES_PER_LAYER;
             if (layer == readyLayer) return;
+#if !(OCEAN_EXP & 256)  // sensitivity bit 256: the column pass does not wait for its rows (what a deferred column pass would see)
             spin_until_ge(a.rowsDone + layer, a.rowsTarget);
+#endif
             fence_proxy_async_global();  // order the acquired generic-proxy writes before the TMA reads
             readyLayer = layer;
         };

@@ -256,3 +256,36 @@ def test_buoyancy_argument_errors(pkg, po):
     assert lib.ocean_buoyancy(body._h, box.ctypes.data, -1, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.ERR_INVALID_ARGUMENT
     assert lib.ocean_buoyancy(body._h, box.ctypes.data, 0, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.OK
     body.OnDisable()
+
+
+@pytest.mark.parametrize("N", [64, 256, 512])
+def test_auto_mips_belong_to_the_frame_that_is_observed(pkg, po, so, N):
+    """ocean_set_auto_mips rebuilds both chains with every frame (WB:191-192).  Whatever the observer (copy_mip,
+    sample_surface, an explicit generate, a sync) and however many frames ran in between, the chains seen are those of the
+    CURRENT frame's arrays, bit for bit -- the contract any other placement of the chain kernels has to keep."""
+    L = pkg._lib
+    cfg, body, _ = stepped_body(pkg, po, n_cfg=2, N=N, frames=1)
+    body.GenerateMips(auto=True)
+    rng = np.random.default_rng(3)
+    pts = rng.uniform(-500, 500, (2000, 2)).astype(np.float32)
+    t = 1.0
+    for burst, observer in ((1, "copy"), (3, "sample"), (2, "generate"), (5, "copy"), (1, "sample"), (4, "sync")):
+        for _ in range(burst):
+            t += 1.0 / 60.0
+            body.CalculateWavesTexturesAtTime(t)
+        if observer == "sample":
+            d, n, f = body.SampleSurface(pts, 1.7)
+            wd, wn, wf = so.surface(body.displacementsTextures, body.derivativesTextures, body.turbulenceTextures, body.wavelengths, pts, 1.7)
+            assert np.array_equal(n, wn) and np.array_equal(f, wf)
+        elif observer == "generate":
+            body.GenerateMips()
+        elif observer == "sync":
+            body.Sync()
+        for which, arr in ((L.DERIVATIVES, body.derivativesTextures), (L.TURBULENCE, body.turbulenceTextures)):
+            want = so.mip_chain(arr[1])
+            for level in (1, 3, body.mipLevels):
+                assert np.array_equal(body.Mip(which, level, 1), want[level]), (observer, which, level)
+    body.GenerateMips(auto=False)
+    body.CalculateWavesTexturesAtTime(t + 1.0)  # chains are now stale by design: level 0 moved on, the chain did not
+    assert not np.array_equal(body.Mip(L.TURBULENCE, 1, 1), so.mip_chain(body.turbulenceTextures[1])[1])
+    body.OnDisable()

@@ -25,6 +25,7 @@ VARIANTS = {
     "f2x1_fast_hot": ["-DOCEAN_F2_EXP=1"],
     "f2x2_no_foam_load": ["-DOCEAN_F2_EXP=2"],
     "f2x3_both": ["-DOCEAN_F2_EXP=3"],
+    "x256_cols_no_await": ["-DOCEAN_EXP=256"],
 }
 if __name__ == "__main__":
     bm = oceanpkg.build_module()

@@ -31,13 +31,19 @@ def tour(N, C, frames=3):
     b.SetReadbackMode(L.READBACK_HEIGHT)
     b.Update(1.0)
     b.WaitReadback()
+    boxes = np.zeros((64, 6), np.float32); boxes[:, :3] = pts[:64].mean() ; boxes[:, 0] = pts[:64, 0]; boxes[:, 2] = pts[:64, 1]; boxes[:, 3:] = 1.0
+    ans = np.zeros((64, 4), np.float32)
+    b.UpdateBuoyancy(1.1, boxes, ans)
+    b.Sync()
+    assert np.isfinite(ans).all()
     b.OnDisable()
     print("tour N=%d C=%d ok" % (N, C), flush=True)
 
 
-tour(64, 2)        # generic row / column kernels
-tour(256, 3)       # fused frame kernel (or rows<256> + cols_tma<256> with OCEAN_FUSED=0)
-tour(512, 1)       # rows<512> + cols_tma<512> (or the fused kernel with OCEAN_FUSED=1)
+SIZES = [int(a) for a in sys.argv[1:]] or [64, 256, 512]
+if 64 in SIZES: tour(64, 2)        # generic row / column kernels
+if 256 in SIZES: tour(256, 3)      # fused frame kernel (or rows<256> + cols_tma<256> with OCEAN_FUSED=0)
+if 512 in SIZES: tour(512, 1)      # rows<512> + cols_tma<512> (or a fused kernel with OCEAN_FUSED=1 / 2)
 oceans, seeds = pkg.scene.ensemble_states(3)
 for fused in ("0", "1"):
     os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = fused
