@@ -618,6 +618,9 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 #ifndef OCEAN_COLS_EARLY_PRODUCER
 #define OCEAN_COLS_EARLY_PRODUCER 0  // 1: an isolated column pass starts 1.1 us sooner, back-to-back frames are 0.2 us slower
 #endif
+#ifndef OCEAN_COLS_REVERSE_LAYERS
+#define OCEAN_COLS_REVERSE_LAYERS 0
+#endif
 #ifndef OCEAN_COLS_TMA_CTAS_PER_SM
 #define OCEAN_COLS_TMA_CTAS_PER_SM 2
 #endif
@@ -644,6 +647,12 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     using Cfg = ColTmaCfg<N>;
     using FFT = typename Cfg::FFT;
     constexpr int T = Cfg::T, W = Cfg::W, TILES_PER_LAYER = N / W;
+    // Tile -> layer.  Build option (off): where the row -> column workspace does not fit L2 (4 x 1024^2: 134 MB against
+    // 126 MB) take the layers in REVERSE order, on the idea that the row pass wrote layer 0 first and the last layers are the
+    // ones still resident.  Measured on B200: 128.0 us per frame against 126.1 in ascending order -- no gain, so ascending
+    // order (columns of layer 0 start while the rows of the last layers are still running) stays everywhere.
+    constexpr bool REVERSE = OCEAN_COLS_REVERSE_LAYERS && N >= 1024;
+    auto layer_of = [&](int tile) { return REVERSE ? a.layers - 1 - tile / TILES_PER_LAYER : tile / TILES_PER_LAYER; };
     extern __shared__ __align__(128) float4 smem[];
     float4* bufA = smem;
     float4* bufB = smem + Cfg::TILE_ELEMS;
@@ -691,7 +700,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 
     // tile -> TMA coordinates: c0 = first fp32 of the tile's columns, c1 = first row
     auto coords = [&](int tile, int& c0, int& c1) {
-        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
+        const int layer = layer_of(tile), xt = tile % TILES_PER_LAYER;
         c0 = xt * W * 4;
         c1 = layer * N;
     };
@@ -702,9 +711,9 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 #if OCEAN_EXP & 64  // sensitivity: launch / dispatch / counter floor -- wait for the rows, publish and leave
     if (threadIdx.x == 0)
         for (int tile = blockIdx.x; tile < totalTiles; tile += gridDim.x) {
-            spin_until_ge(a.rowsDone + tile / TILES_PER_LAYER, a.rowsTarget);
+            spin_until_ge(a.rowsDone + layer_of(tile), a.rowsTarget);
             __threadfence();
-            atomicAdd(a.colsDone + tile / TILES_PER_LAYER, (unsigned long long)W);
+            atomicAdd(a.colsDone + layer_of(tile), (unsigned long long)W);
         }
     return;
 #endif
@@ -748,7 +757,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         };
         int readyLayer = -1;  // layers are polled once: counters only grow
         auto await_rows = [&](int tile) {
-            const int layer = tile / TILES_PER_LAYER;
+            const int layer = layer_of(tile);
             if (layer == readyLayer) return;
 #if !(OCEAN_EXP & 256)  // sensitivity bit 256: the column pass does not wait for its rows (what a deferred column pass would see)
             spin_until_ge(a.rowsDone + layer, a.rowsTarget);
@@ -789,7 +798,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
                     sv += ckPart[w * 3 + 1];
                     st += ckPart[w * 3 + 2];
                 }
-                unsigned long long* out = a.checksums + (size_t)((tile / TILES_PER_LAYER) / a.C) * 3;
+                unsigned long long* out = a.checksums + (size_t)(layer_of(tile) / a.C) * 3;
                 atomicAdd(out + 0, sd);
                 atomicAdd(out + 1, sv);
                 atomicAdd(out + 2, st);
@@ -804,7 +813,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             bulk_wait_all();
             fence_proxy_async_global();
             __threadfence();
-            atomicAdd(a.colsDone + tile / TILES_PER_LAYER, (unsigned long long)W);
+            atomicAdd(a.colsDone + layer_of(tile), (unsigned long long)W);
         }
         return;
     }
@@ -816,7 +825,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     const bool zeroFoam = a.zeroFoam != 0 || (OCEAN_EXP & 4);
     uint32_t parity = 0;
     for (int tile = blockIdx.x; tile < totalTiles; tile += gridDim.x, parity ^= 1) {
-        const int layer = tile / TILES_PER_LAYER, xt = tile - layer * TILES_PER_LAYER;
+        const int layer = layer_of(tile), xt = tile % TILES_PER_LAYER;
         const int x = xt * W + xw;
         // Permute FFT:73-78: (x + y) % 2 with y = tid + T*j and T even  =>  parity of x + tid
         const Epilogue ep(((x + tid) & 1) ? -1.0f : 1.0f, lambda);

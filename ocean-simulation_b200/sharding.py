@@ -48,3 +48,34 @@ def torch_all_gather(device=None):
         return [p.cpu().numpy().view(np.uint64) for p in parts]
 
     return gather
+
+
+class _DeviceArray:
+    """A library-owned device array (ocean_get_output) as a __cuda_array_interface__ object: torch.as_tensor(...) then
+    views the library's memory without a copy, so NCCL can send it straight over NVLink."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(int(s) for s in shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+def device_view(body, which):
+    """torch view (no copy) of one output array of a WaterBody: [C][N][N][4] float32 on the body's device.
+    The caller orders its use after the frame (body.Sync(), or work on the body's stream)."""
+    import torch
+    ptr, nbytes = body.device_pointer(which)
+    C, N = len(body.cascades), body.texturesSize
+    assert nbytes == C * N * N * 16
+    return torch.as_tensor(_DeviceArray(ptr, (C, N, N, 4)), device=torch.device("cuda", body.device))
+
+
+def all_gather_arrays(local, world=None):
+    """The optional final gather of SURVEY 8(e): every rank contributes one tensor of the same shape (an output array of
+    the ocean it owns: device_view(...) on GPUs -> NCCL over NVLink / NVSwitch; a CPU tensor under gloo) and receives
+    [world][...] with rank r's array at index r.  Off the hot path: 16 MiB per 4 x 512^2 array per rank."""
+    import torch
+    import torch.distributed as dist
+    world = world or dist.get_world_size()
+    out = torch.empty((world,) + tuple(local.shape), dtype=local.dtype, device=local.device)
+    dist.all_gather([out[r] for r in range(world)], local.contiguous())  # (views of `out`: no extra copy; works under gloo too)
+    return out

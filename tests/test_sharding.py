@@ -33,6 +33,12 @@ def run_states(oc, sd):
 
 got = pkg.sharding.run_sharded(run_states, oceans, seeds, rank, world, gather=pkg.sharding.torch_all_gather())
 np.save(sys.argv[4] + ".rank%%d.npy" %% rank, got)
+# the optional final gather of an output ARRAY (SURVEY 8e): rank r contributes the displacement of state r
+import torch
+b = po.OracleB(N, tuple(float(v) for v in oceans[rank]), casc, po.fill_noise(int(seeds[rank]), N))
+b.init_spectrum(); b.step(1.0)
+arrays = pkg.sharding.all_gather_arrays(torch.from_numpy(b.get(po.DISP)))
+np.save(sys.argv[4] + ".arrays%%d.npy" %% rank, arrays.numpy())
 mine = pkg.sharding.shard_indices(7, rank, world)
 print("rank", rank, "owns", mine.tolist())
 dist.barrier(); dist.destroy_process_group()
@@ -73,3 +79,11 @@ def test_world_size_2_gloo_gather_equals_serial(tmp_path, po, pkg):
     serial = pkg.sharding.run_sharded(run_states, oceans, seeds)
     assert np.array_equal(serial, a)
     assert len(set(a[:, 0].tolist())) == 7  # seven different oceans
+    # gathered output arrays: [world][C][N][N][4], identical on both ranks, rank r's ocean at index r
+    g0, g1 = np.load(prefix + ".arrays0.npy"), np.load(prefix + ".arrays1.npy")
+    assert g0.shape == (2, 3, N, N, 4) and np.array_equal(g0, g1)
+    for r in range(2):
+        ob = po.OracleB(N, tuple(float(v) for v in oceans[r]), casc, po.fill_noise(int(seeds[r]), N))
+        ob.init_spectrum()
+        ob.step(1.0)
+        assert np.array_equal(g0[r], ob.get(po.DISP))
