@@ -179,6 +179,15 @@ __device__ __forceinline__ void checksum_flush(unsigned long long* out, unsigned
 #ifndef OCEAN_EXP
 #define OCEAN_EXP 0
 #endif
+// (1/|k|, omega) recomputed instead of loaded (see wave_hot in ocean_fused2.cuh): 8 B per texel-cascade less HBM traffic
+#ifndef OCEAN_ROWS_RECOMPUTE_HOT
+#define OCEAN_ROWS_RECOMPUTE_HOT 0
+#endif
+__device__ __forceinline__ float2 rows_wave_hot(float kx, float kz, float gravity) {
+    const float kMag = __fsqrt_rn(__fadd_rn(__fmul_rn(kx, kx), __fmul_rn(kz, kz)));
+    const float ik = kMag > 0.0f ? __frcp_rn(kMag) : 1.0f;
+    return make_float2(ik, __fsqrt_rn(__fmul_rn(gravity, kMag)));
+}
 template <int N> struct RowCfg {
     static constexpr int T = N / 8;
     static constexpr int R = (N == 512) ? OCEAN_ROWS512_R : ((T >= 64) ? 1 : 64 / T);  // rows per CTA
@@ -263,7 +272,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     for (int j = 0; j < 8; ++j) {
         const int x = tid + T * j;
         cp_async16(&hs[FFT::template phys<0>(x, row)], H + x);
+#if !OCEAN_ROWS_RECOMPUTE_HOT
         wreg[j] = ld_once(Wd + x);
+#endif
     }
 #else
 #pragma unroll
@@ -285,12 +296,14 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     for (int j = 0; j < 8; ++j) {
         const int x = tid + T * j;
         const float4 h0 = hs[FFT::template phys<0>(x, row)];
-#if OCEAN_ROWS_WAVE_REGS
+        const float kx = (float)(x - N / 2) * dk;  // IS:111 (waveData.x)
+#if OCEAN_ROWS_RECOMPUTE_HOT
+        const float2 wv = rows_wave_hot(kx, kz, a.states ? a.states[layer / a.C].gravity : a.gravity);
+#elif OCEAN_ROWS_WAVE_REGS
         const float2 wv = wreg[j];
 #else
         const float2 wv = ws[row * N + x];
 #endif
-        const float kx = (float)(x - N / 2) * dk;  // IS:111 (waveData.x)
         evolve_texel(h0, wv, kx, kz, time, pa[j], pb[j]);
     }
 
