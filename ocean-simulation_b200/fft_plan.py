@@ -142,3 +142,62 @@ def run_plan(x, W=1, check_conflicts=False, dense0=False):
     for j in range(8):
         X[:, tid + T * j] = reg[j].T
     return X, conflicts
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Shared-memory wavefronts of one column tile, instruction by instruction (ocean_cols_tma_kernel, compute warps).
+# A wavefront is one 128-byte pass of the shared-memory pipe; a warp-wide access needs as many passes as the busiest
+# bank has distinct 4-byte words (identical addresses are broadcast).  `ideal` is what ncu's source page calls
+# "L1 Wavefronts Shared Ideal": ceil(distinct bytes / 128).  tests/test_fft_plan.py compares the totals with the
+# per-instruction counters of the committed ncu capture (profiles/r2_ncu_smem_by_instruction.txt).
+
+def warp_wavefronts(byte_addresses, access_bytes):
+    """(wavefronts, ideal) of one warp-wide shared-memory instruction.  byte_addresses: 32 lane addresses."""
+    words = set()
+    for a in byte_addresses:
+        for k in range(access_bytes // 4):
+            words.add(int(a) // 4 + k)
+    per_bank = np.bincount([w % 32 for w in words], minlength=32)
+    return int(per_bank.max()), -(-len(words) * 4 // 128)
+
+
+def column_tile_wavefronts(N=512, W=4):
+    """LSU wavefronts per tile of the TMA column kernel by instruction class: {class: (wavefronts, ideal)}.
+    Thread = (tid, xw), lane = xw + W * tid; element e of a tile buffer sits at byte 16 * e (exchange 0 dense, exchange
+    1.. swizzled); twiddles are float2 [(stage*7 + q-1) * T + tid]."""
+    T, S = N // 8, len(stage_radices(N))
+    threads = W * T
+    out = {}
+
+    def add(kind, addr_fn, nbytes, count=1):
+        for w0 in range(0, threads, 32):
+            lanes = range(w0, w0 + 32)
+            wf, ideal = warp_wavefronts([addr_fn(l // W, l % W) for l in lanes], nbytes)
+            a = out.setdefault(kind, [0, 0])
+            a[0] += wf * count
+            a[1] += ideal * count
+
+    for plane in range(2):
+        for j in range(8):  # initial loads of the TMA-staged tile and the final staging stores: element (tid + T*j) * W + xw
+            add("LDS.128", lambda tid, xw, j=j: 16 * ((tid + T * j) * W + xw), 16)
+            add("STS.128", lambda tid, xw, j=j: 16 * ((tid + T * j) * W + xw), 16)
+        for s in range(S - 1):
+            Cs = 8 ** s
+            Ms = N // Cs
+            Mn = Ms // 8
+            for q in range(8):  # exchange stores: logical F = tid + T*q (ocean_fft.cuh stage<s>)
+                add("STS.128", lambda tid, xw, q=q, s=s: 16 * swizzle((tid + T * q) * W + xw, s, True), 16)
+            rn = stage_radices(N)[s + 1]
+            for j in range(8):
+                if rn == 8:
+                    Q = Mn // 8
+                    add("LDS.128", lambda tid, xw, j=j, s=s, Q=Q: 16 * swizzle((((tid // Q) * 8 + j) * Q + tid % Q) * W + xw, s, True), 16)
+                else:
+                    i, jj = divmod(j, rn)
+                    add("LDS.128", lambda tid, xw, i=i, jj=jj, s=s, rn=rn: 16 * swizzle(((tid + T * i) * rn + jj) * W + xw, s, True), 16)
+            for q in range(1, 8):  # twiddles of the stage that precedes this exchange
+                add("LDS.64", lambda tid, xw, q=q, s=s: 8 * ((s * 7 + q - 1) * T + tid), 8)
+    for j in range(8):  # plane B's epilogue: incoming foam = .x of the staged RGBA turbulence texel, outgoing texel
+        add("LDS.32", lambda tid, xw, j=j: 16 * ((tid + T * j) * W + xw), 4)
+        add("STS.128", lambda tid, xw, j=j: 16 * ((tid + T * j) * W + xw), 16)
+    return {k: tuple(v) for k, v in out.items()}

@@ -44,3 +44,17 @@ def test_headline_layouts_are_bank_conflict_free():
     assert _worst(256, 8, True) == 1
     # generic column kernel (swizzled everywhere) at its default widths: at most 2-way
     assert _worst(1024, 2, False) <= 2 and _worst(2048, 2, False) <= 2 and _worst(128, 8, False) == 1
+
+
+def test_column_tile_wavefronts_match_the_ncu_source_page():
+    """The conflict model extended from the exchanges to every shared-memory instruction of a column tile.  The figures are
+    those of the committed ncu capture, per tile (profiles/r2_ncu_smem_by_instruction.txt: 512 tiles per launch): everything
+    is conflict-free except the scalar read of the incoming turbulence .x from the staged RGBA tile (4-way, by layout)."""
+    got = plan.column_tile_wavefronts(512, 4)
+    ncu_per_launch = {"LDS.128": (786432, 786432), "STS.128": (917504, 917504), "LDS.64": (114688, 114688), "LDS.32": (131072, 32768)}
+    assert got == {k: (w // 512, i // 512) for k, (w, i) in ncu_per_launch.items()}
+    excess = sum(w - i for w, i in got.values())
+    assert excess == 192 == 8 * 8 * 3  # eight foam reads per thread, eight warps per tile, three extra wavefronts each
+    for W in (2, 8):  # other tile widths: the transform itself stays conflict-free
+        g = plan.column_tile_wavefronts(512, W)
+        assert g["LDS.128"][0] == g["LDS.128"][1] and g["STS.128"][0] == g["STS.128"][1]
