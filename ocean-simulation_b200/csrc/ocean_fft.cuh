@@ -82,6 +82,9 @@ __device__ __forceinline__ C2 c2_load(const float4* p) {
 __device__ __forceinline__ void c2_store(float4* p, const C2& v) { *reinterpret_cast<ulonglong2*>(p) = make_ulonglong2(v.re, v.im); }
 
 #define OCEAN_SQRT1_2 0.70710678118654752440f
+#ifndef OCEAN_HETERO_BASE
+#define OCEAN_HETERO_BASE 288  // threads of the column role (256 compute + producer warp) in the heterogeneous frame kernel
+#endif
 
 // Inverse DFT-4: o[q] = sum_j c[j] e^{+2 pi i j q / 4}
 __device__ __forceinline__ void radix4_inv(const C2& c0, const C2& c1, const C2& c2, const C2& c3, C2& o0, C2& o1, C2& o2, C2& o3) {
@@ -151,7 +154,11 @@ struct LineFFT {
 
     __device__ static __forceinline__ void barrier() {
         if constexpr (BAR_THREADS > 0) asm volatile("bar.sync 1, %0;" ::"n"(BAR_THREADS) : "memory");
-        else __syncthreads();
+        else if constexpr (BAR_THREADS < 0) {
+            // line groups of -BAR_THREADS threads that follow the first OCEAN_HETERO_BASE threads of the CTA, one named
+            // barrier (2, 3, ...) per group (heterogeneous frame kernel, ocean_hetero.cuh)
+            asm volatile("bar.sync %0, %1;" ::"r"(2 + ((int)threadIdx.x - OCEAN_HETERO_BASE) / (-BAR_THREADS)), "n"(-BAR_THREADS) : "memory");
+        } else __syncthreads();
     }
     __device__ static __forceinline__ float2 twiddle(const float2* __restrict__ tw, int i) {
         if constexpr (TW_SMEM) return tw[i];

@@ -909,6 +909,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
 
 #include "ocean_fused.cuh"
 #include "ocean_fused2.cuh"
+#include "ocean_hetero.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // WaterBody.GetWaterHeight WB:195-209 (mode 0), plus bilinear extensions at the shader's own
@@ -1121,6 +1122,26 @@ template <int N> static int frame2_grid(int layers) {
 template <int N> static cudaError_t frame2_launch(const FrameArgs& a, const ColsTmaMaps& m, cudaStream_t s, bool early) {
     using Cfg = Fused2Cfg<N>;
     return launch_pdl(early, a, ocean_frame2_kernel<N>, dim3(frame2_grid<N>(a.layers)), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, s, m, a);
+}
+// Probe: both roles in one persistent CTA per SM (ocean_hetero.cuh).  mode 1: in order (column team waits for its rows:
+// results identical to the two-kernel frame), mode 2: column team does not wait (timing of a deferred schedule; WRONG results).
+int hetero_mode(int N, const ColsTmaMaps* maps) {
+    static const int mode = [] { const char* e = getenv("OCEAN_HETERO"); return e ? atoi(e) : 0; }();
+    return (N == 512 && maps && maps->valid) ? mode : 0;
+}
+cudaError_t launch_hetero(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, int mode) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(ocean_hetero_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, HeteroCfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(ocean_hetero_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, HeteroCfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    const int totalTiles = a.layers * (HeteroCfg::N / HeteroCfg::W);
+    const int grid = num_sms();
+    if (mode == 2) return launch_pdl(true, a, ocean_hetero_kernel<false>, dim3(grid), dim3(HeteroCfg::THREADS), HeteroCfg::SMEM_BYTES, s, *maps, a, a, totalTiles);
+    return launch_pdl(true, a, ocean_hetero_kernel<true>, dim3(grid), dim3(HeteroCfg::THREADS), HeteroCfg::SMEM_BYTES, s, *maps, a, a, totalTiles);
 }
 static bool tma_size(int N) { return N == 256 || N == 512 || N == 1024; }
 // The whole frame as one persistent kernel.  Mode 1 (static round robin) was the default at N = 256 in round 1, where the

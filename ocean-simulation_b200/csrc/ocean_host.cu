@@ -472,6 +472,12 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which, float* heig
         ++frame;
         return autoMips ? GenerateMips() : OCEAN_OK;
     }
+    if (which == 0 && !auxSignals && !autoMips && hetero_mode(N, &colsMaps)) {
+        OCEAN_CUDA(launch_hetero(a, &colsMaps, stream, hetero_mode(N, &colsMaps)));
+        foamZero = false;
+        ++frame;
+        return OCEAN_OK;
+    }
     if (doRows) {
         OCEAN_CUDA(launch_rows(a, stream, true));  // every producer of h0/waveHot was synchronised
         rowsPending = true;

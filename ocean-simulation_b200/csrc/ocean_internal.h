@@ -137,6 +137,8 @@ cudaError_t launch_cols(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_
 int frame_fused_mode(int N, const ColsTmaMaps* maps);
 int frame_fused_grid(int N, int layers, int mode);  // persistent grid size of that kernel (FrameArgs::itemBase arithmetic)
 bool rows_need_h0c();  // the selected row pass reads FrameArgs::h0c / InitArgs::h0c (else they stay nullptr)
+int hetero_mode(int N, const ColsTmaMaps* maps);  // probe (OCEAN_HETERO): both roles in one persistent CTA per SM
+cudaError_t launch_hetero(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, int mode);
 cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, bool early, int mode);
 cudaError_t launch_query(const float4* disp, int N, int C, const float* wavelengths /*host, C*/, const float2* pts,
                          float* out, int n, int mode, cudaStream_t s);

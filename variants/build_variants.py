@@ -26,6 +26,10 @@ VARIANTS = {
     "f2x2_no_foam_load": ["-DOCEAN_F2_EXP=2"],
     "f2x3_both": ["-DOCEAN_F2_EXP=3"],
     "x256_cols_no_await": ["-DOCEAN_EXP=256"],
+    "hetero_g4": ["-DOCEAN_HETERO_G=4"],
+    "hetero_g5": ["-DOCEAN_HETERO_G=5"],
+    "hetero_g6": ["-DOCEAN_HETERO_G=6"],
+    "hetero_g7": ["-DOCEAN_HETERO_G=7"],
     "rows_recompute_hot": ["-DOCEAN_ROWS_RECOMPUTE_HOT=1"],
     "cols_reverse_1024": ["-DOCEAN_COLS_REVERSE_LAYERS=1"],
 }
