@@ -11,8 +11,8 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize("env", [{}, {"OCEAN_ROWS_PAIR": "1"}, {"OCEAN_FUSED": "1"}, {"OCEAN_FUSED": "0"}, {"OCEAN_NO_PDL": "1"}],
-                         ids=["default", "pair-rows", "fused-frame", "two-kernel-frame", "no-pdl"])
+@pytest.mark.parametrize("env", [{}, {"OCEAN_ROWS_PAIR": "1"}, {"OCEAN_FUSED": "1"}, {"OCEAN_FUSED": "2"}, {"OCEAN_HETERO": "1"}, {"OCEAN_FUSED": "0"}, {"OCEAN_NO_PDL": "1"}],
+                         ids=["default", "pair-rows", "fused-frame", "fused-frame-dynamic", "hetero-frame", "two-kernel-frame", "no-pdl"])
 def test_variant_matches_oracle(pkg, po, env):
     r = subprocess.run([sys.executable, os.path.join(HERE, "_variant_check.py")], env=dict(os.environ, **env),
                        capture_output=True, text=True, timeout=600)
