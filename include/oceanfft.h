@@ -204,6 +204,23 @@ typedef struct OceanBuoyantBox {
 int ocean_buoyancy(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode /*OceanQueryMode*/, float density,
                    float gravityY, float* out4, int boxesOnDevice, int outOnDevice);
 
+/* ocean_buoyancy without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same kernels and bit-identical results as ocean_buoyancy, but the intermediate arrays of the chain (query
+ * points, heights, and the staging of boxes / answers when they live in host memory) sit in a file-scope
+ * `static __device__ __align__(256)` array of the library instead of cudaMalloc'ed scratch: the call makes no cudaMalloc,
+ * cudaFree or allocating library call.  Limits and rules:
+ *   - n <= OCEAN_NOALLOC_MAX_BOXES; a larger n is rejected with OCEAN_ERR_INVALID_ARGUMENT (split the batch);
+ *   - the array is 52 B x OCEAN_NOALLOC_MAX_BOXES = 3.25 MiB and every GPU that loads the library holds it until exit;
+ *   - every handle on a device shares the array and it keeps the previous call's contents; each call overwrites every slot
+ *     it later reads, so nothing needs clearing, but two calls that OVERLAP ON THE GPU (handles on different streams) race:
+ *     serialise them (one stream, or ocean_sync between them);
+ *   - with host buffers the call returns when out4 is filled; with device pointers it is asynchronous on the handle's
+ *     stream, exactly as ocean_buoyancy. */
+#define OCEAN_NOALLOC_MAX_BOXES 65536
+int ocean_buoyancy_noalloc(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode /*OceanQueryMode*/, float density,
+                           float gravityY, float* out4, int boxesOnDevice, int outOnDevice);
+
 /* WaterBody.Update (WB:284-297) + BuoyantObject.FixedUpdate (BO:18-30) with the queries answered on the owning GPU:
  * one frame at `time`, then -- on the handle's copy stream, released as soon as the columns of layer 0 are done -- the n
  * boxes are copied to the device, looked up in that frame's height plane exactly as OCEAN_QUERY_NEAREST_REF does

@@ -17,6 +17,7 @@ READBACK_RGBA, READBACK_HEIGHT = range(2)
 # OceanQueryMode
 QUERY_NEAREST_REF, QUERY_READBACK_REF, QUERY_BILINEAR, QUERY_BILINEAR_ALL_CASCADES, QUERY_DISPLACED = range(5)
 DISPLACED_ITERATIONS = 4
+NOALLOC_MAX_BOXES = 65536  # OCEAN_NOALLOC_MAX_BOXES
 
 # every symbol include/oceanfft.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = [
@@ -29,6 +30,7 @@ ABI_SYMBOLS = [
     "ocean_ensemble_get_output", "ocean_ensemble_copy_output",
     "ocean_generate_mips", "ocean_set_auto_mips", "ocean_mip_levels", "ocean_get_mips", "ocean_copy_mip",
     "ocean_sample_surface", "ocean_buoyancy", "ocean_update_buoyancy", "ocean_get_copy_stream",
+    "ocean_buoyancy_noalloc",
 ]
 
 
@@ -114,6 +116,7 @@ def load():
     L.ocean_buoyancy.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp, ctypes.c_int, ctypes.c_int]
     L.ocean_update_buoyancy.argtypes = [vp, ctypes.c_float, vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp]
     L.ocean_get_copy_stream.argtypes = [vp, ctypes.POINTER(vp)]
+    L.ocean_buoyancy_noalloc.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp, ctypes.c_int, ctypes.c_int]
     _lib = L
     return L
 

@@ -283,6 +283,39 @@ static cudaError_t stream_wait_value_geq(cudaStream_t s, const unsigned long lon
     return r == 0 ? cudaSuccess : cudaErrorUnknown;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch of ocean_buoyancy_noalloc (no counterpart in the reference): callers
+// that may not allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc -- get the
+// buoyancy chain (gather of the query points -> height query -> BO:19-29) with its intermediate arrays in this file-scope
+// device array instead of OceanHandle::bBuf.  Layout, for MAX = OCEAN_NOALLOC_MAX_BOXES boxes (52 B per box, 3.25 MiB;
+// every GPU that loads the library holds it until the process exits):
+//     float4 answers[MAX] | float2 points[MAX] | float heights[MAX] | OceanBuoyantBox boxes[MAX]
+// (answers / boxes are only used as staging when the caller's buffers live in host memory).
+// In HOST code the name `g_noallocScratch` is a host-side stand-in, NOT a device address: handing it to a kernel faults,
+// or silently uses the wrong memory where the GPU can reach host memory.  noalloc_scratch() therefore asks the runtime for
+// the device address -- once per device, with that device current -- and caches it.
+constexpr size_t kNoallocBytesPerBox = sizeof(float4) + sizeof(float2) + sizeof(float) + sizeof(OceanBuoyantBox);
+static __device__ __align__(256) unsigned char g_noallocScratch[(size_t)OCEAN_NOALLOC_MAX_BOXES * kNoallocBytesPerBox];
+
+static std::mutex g_noallocMutex;
+static void* g_noallocPtr[64] = {};
+
+// Device address of the scratch on `device`, which must be the current device.
+static cudaError_t noalloc_scratch(int device, void** out) {
+    *out = nullptr;
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocPtr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noallocScratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_noallocPtr[device] = p;
+    }
+    *out = g_noallocPtr[device];
+    return cudaSuccess;
+}
+
 }  // namespace ocean
 
 using namespace ocean;
@@ -371,6 +404,8 @@ struct OceanHandle {
     int AttachWorkspace(cudaStream_t shared);
     int GenerateMips();
     int Buoyancy(const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4, bool boxesDev, bool outDev);
+    int BuoyancyNoAlloc(const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4, bool boxesDev,
+                        bool outDev);
     int SampleSurface(const float* worldXZ, int n, float lod, float* disp3, float* normal3, float* foam, bool onDevice);
     void OnDisable();
 };
@@ -522,6 +557,43 @@ int OceanHandle::Buoyancy(const OceanBuoyantBox* boxes, int n, int mode, float d
     float2* dPts = (float2*)(dOut + n);
     float* dHeights = (float*)(dPts + n);
     OceanBuoyantBox* dBoxes = (OceanBuoyantBox*)(dHeights + n);
+    const OceanBuoyantBox* bx = boxes;
+    if (!boxesDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(dBoxes, boxes, (size_t)n * sizeof(OceanBuoyantBox), cudaMemcpyHostToDevice, stream));
+        bx = dBoxes;
+    }
+    OCEAN_CUDA(launch_buoyancy_points(bx, dPts, n, stream));
+    float wl[OCEAN_MAX_CASCADES];
+    for (int i = 0; i < C; ++i) wl[i] = cascades[i].wavelength;
+    if (mode == OCEAN_QUERY_DISPLACED) {
+        OCEAN_CUDA(launch_displaced_query(disp, N, C, wl, dPts, dHeights, n, OCEAN_DISPLACED_ITERATIONS, stream));
+    } else {
+        OCEAN_CUDA(launch_query(disp, N, C, wl, dPts, dHeights, n, mode, stream));
+    }
+    float4* out = outDev ? (float4*)out4 : dOut;
+    OCEAN_CUDA(launch_buoyancy(bx, dHeights, n, density, gravityY, out, stream));
+    if (!outDev) {
+        OCEAN_CUDA(cudaMemcpyAsync(out4, dOut, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, stream));
+        OCEAN_CUDA(cudaStreamSynchronize(stream));
+    }
+    return OCEAN_OK;
+}
+
+// OceanHandle::Buoyancy with every intermediate in the static device array above: no cudaMalloc / cudaFree, no allocating
+// library call.  Same kernels, same launch order, same results.  Every slot of the scratch that a kernel reads was written
+// earlier in the same call (points and heights for i < n; the staged boxes by the copy), so nothing has to start at zero and
+// the previous call's contents are simply overwritten.  The array is shared by every handle of the process on this device:
+// two calls that overlap on the GPU (different streams) race on it.
+int OceanHandle::BuoyancyNoAlloc(const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4,
+                                 bool boxesDev, bool outDev) {
+    if (n == 0) return OCEAN_OK;
+    void* base = nullptr;
+    OCEAN_CUDA(noalloc_scratch(device, &base));
+    const size_t MAX = OCEAN_NOALLOC_MAX_BOXES;
+    float4* dOut = (float4*)base;
+    float2* dPts = (float2*)(dOut + MAX);
+    float* dHeights = (float*)(dPts + MAX);
+    OceanBuoyantBox* dBoxes = (OceanBuoyantBox*)(dHeights + MAX);
     const OceanBuoyantBox* bx = boxes;
     if (!boxesDev) {
         OCEAN_CUDA(cudaMemcpyAsync(dBoxes, boxes, (size_t)n * sizeof(OceanBuoyantBox), cudaMemcpyHostToDevice, stream));
@@ -1180,6 +1252,20 @@ int ocean_buoyancy(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode
     if (!h->spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_buoyancy before ocean_init_spectrum");
     DeviceScope scope(h->device);
     return h->Buoyancy(boxes, n, mode, density, gravityY, out4, boxesOnDevice != 0, outOnDevice != 0);
+}
+
+int ocean_buoyancy_noalloc(OceanHandle* h, const OceanBuoyantBox* boxes, int n, int mode, float density, float gravityY, float* out4,
+                           int boxesOnDevice, int outOnDevice) {
+    if (!h || (n > 0 && (!boxes || !out4))) return fail(OCEAN_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (n < 0) return fail(OCEAN_ERR_INVALID_ARGUMENT, "n < 0");
+    if (n > OCEAN_NOALLOC_MAX_BOXES)
+        return fail(OCEAN_ERR_INVALID_ARGUMENT, "ocean_buoyancy_noalloc: n = %d exceeds OCEAN_NOALLOC_MAX_BOXES = %d (the fixed scratch of the "
+                    "allocation-free path); split the batch or use ocean_buoyancy", n, OCEAN_NOALLOC_MAX_BOXES);
+    if (mode < OCEAN_QUERY_NEAREST_REF || mode > OCEAN_QUERY_DISPLACED || mode == OCEAN_QUERY_READBACK_REF)
+        return fail(OCEAN_ERR_INVALID_ARGUMENT, "ocean_buoyancy_noalloc takes a device query mode (not %d; READBACK_REF is a host lookup)", mode);
+    if (!h->spectrumReady) return fail(OCEAN_ERR_NOT_INITIALIZED, "ocean_buoyancy_noalloc before ocean_init_spectrum");
+    DeviceScope scope(h->device);
+    return h->BuoyancyNoAlloc(boxes, n, mode, density, gravityY, out4, boxesOnDevice != 0, outOnDevice != 0);
 }
 
 int ocean_generate_mips(OceanHandle* h) {

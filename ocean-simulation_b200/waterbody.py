@@ -200,6 +200,15 @@ class WaterBody:
                                          out.ctypes.data, 0, 0))
         return out
 
+    def BuoyancyNoAlloc(self, boxes, mode=L.QUERY_NEAREST_REF, density=1.0, gravityY=-9.81):
+        """Buoyancy() through ocean_buoyancy_noalloc: same results, no allocation inside the library (scratch in a static
+        device array; at most L.NOALLOC_MAX_BOXES boxes per call; calls that overlap on the GPU race on that array)."""
+        b = np.ascontiguousarray(boxes, np.float32).reshape(-1, 6)
+        out = np.empty((b.shape[0], 4), np.float32)
+        L.check(self._lib.ocean_buoyancy_noalloc(self._need(), b.ctypes.data, b.shape[0], int(mode), float(density), float(gravityY),
+                                                 out.ctypes.data, 0, 0))
+        return out
+
     def UpdateBuoyancy(self, time, boxes, out, density=1.0, gravityY=-9.81):
         """WaterBody.Update + BuoyantObject.FixedUpdate with the lookups answered on the owning GPU (ocean_update_buoyancy).
         boxes: float32 [n][6] and out: float32 [n][4], caller-owned (pinned for overlap) and untouched until Sync().

@@ -36,7 +36,7 @@ static const void* const kSymbols[] = {
     (const void*)ocean_get_stream, (const void*)ocean_set_stream, (const void*)ocean_launch_count, (const void*)ocean_describe,
     (const void*)ocean_ensemble_create, (const void*)ocean_ensemble_destroy, (const void*)ocean_ensemble_run,
     (const void*)ocean_ensemble_get_output, (const void*)ocean_ensemble_copy_output, (const void*)ocean_update_buoyancy,
-    (const void*)ocean_get_copy_stream,
+    (const void*)ocean_get_copy_stream, (const void*)ocean_buoyancy_noalloc,
 };
 
 static const OceanCascade kCascades[2] = {{1530.0f, 1e-10f, 1e12f, 0.4f, 0.1f}, {201.0f, 1e-5f, 1e6f, 0.1f, 0.1f}};
