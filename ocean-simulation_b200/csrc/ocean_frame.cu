@@ -214,17 +214,21 @@ template <int N> struct ColCfg {
 
 // ---------------------------------------------------------------------------------------------
 // workspace stores of the row pass
-__device__ __forceinline__ void ws_store(float4* p, const C2& v) {
+__device__ __forceinline__ void ws_store(float4* p, const C2& v, const uint64_t policy = L2_EVICT_LAST) {
 #if OCEAN_EXP & 8
     if (v.re == 0x123456789abcdefull) c2_store(p, v);  // sensitivity: (practically) never stores
     return;
 #endif
 #if OCEAN_L2_HINTS & 4
-    c2_store_hint(p, v, L2_EVICT_LAST);
+    c2_store_hint(p, v, policy);
 #else
     c2_store(p, v);
 #endif
 }
+// Workspace residency per layer (FrameArgs::wsResident): the planes of the first `wsResident` layers are stored evict_last
+// (they are to stay in L2 until the column pass has read them), the planes of the other layers evict_first (they do not
+// fit anyway -- 4 x 1024^2 has 134 MB of planes against 126 MB of L2 -- and streaming them keeps the resident ones resident).
+__device__ __forceinline__ uint64_t ws_policy(const FrameArgs& a, int layer) { return layer < a.wsResident ? L2_EVICT_LAST : L2_EVICT_FIRST; }
 
 template <int N>
 __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_rows_kernel(const FrameArgs a) {
@@ -285,6 +289,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     }
 #endif
     const int layer = (int)(line / N), y = (int)(line & (N - 1));
+    const uint64_t wsPol = ws_policy(a, layer);
     const float dk = a.dk[layer % a.C];
     const float kz = (float)(y - N / 2) * dk;  // IS:111 (waveData.z)
     const float time = a.time;
@@ -321,9 +326,9 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
         float4* __restrict__ outA = a.rowsA + line * N;
         float4* __restrict__ outB = a.rowsB + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ws_store(&outA[tid + T * j], pa[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&outA[tid + T * j], pa[j], wsPol);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ws_store(&outB[tid + T * j], pb[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&outB[tid + T * j], pb[j], wsPol);
     }
     TRACE(0, blockIdx.x, 5);
     TRACE(0, blockIdx.x, 6);
@@ -339,7 +344,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (active) {
         float4* __restrict__ out = a.rowsA + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pa[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pa[j], wsPol);
     }
     TRACE(0, blockIdx.x, 5);
     FFT::run(pb, smem, tid, row, a.twiddle, FFT::EXCHANGES);
@@ -347,7 +352,7 @@ __global__ void __launch_bounds__(RowCfg<N>::THREADS, RowCfg<N>::MINB) ocean_row
     if (active) {
         float4* __restrict__ out = a.rowsB + line * N;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pb[j]);
+        for (int j = 0; j < 8; ++j) ws_store(&out[tid + T * j], pb[j], wsPol);
     }
 #endif
     // publish: this CTA's rows of both planes are in memory (visible to the TMA loads of the column pass)
@@ -741,7 +746,8 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
             for (int b = 0; b < Cfg::NBOX; ++b) {
                 float4* dst = buf + b * Cfg::BOX_ROWS * W;
                 const int r0 = c1 + b * Cfg::BOX_ROWS;
-                if ((OCEAN_L2_HINTS & 1) && !isTurb) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_LAST);       // workspace: stays put
+                if (!isTurb && layer_of(tile) >= a.wsResident) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_FIRST);  // streamed layer: read once
+                else if ((OCEAN_L2_HINTS & 1) && !isTurb) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_LAST);       // workspace: stays put
                 else if ((OCEAN_L2_HINTS & 8) && isTurb) tma_load_2d_hint(dst, map, bar, c0, r0, L2_EVICT_FIRST);  // read once
                 else tma_load_2d(dst, map, bar, c0, r0);
             }
@@ -1154,12 +1160,20 @@ static bool tma_size(int N) { return N == 256 || N == 512 || N == 1024; }
 #ifndef OCEAN_FUSED_DEFAULT_512
 #define OCEAN_FUSED_DEFAULT_512 0
 #endif
+#ifndef OCEAN_FUSED_DEFAULT_1024
+#define OCEAN_FUSED_DEFAULT_1024 0
+#endif
 int frame_fused_mode(int N, const ColsTmaMaps* maps) {
-    if (!(N == 256 || N == 512) || !maps || !maps->valid) return 0;
+    if (!(N == 256 || N == 512 || N == 1024) || !maps || !maps->valid) return 0;
     static const int mode = [] {
         const char* e = getenv("OCEAN_FUSED");
         return e == nullptr ? -1 : (e[0] - '0');
     }();
+    if (N == 1024) {  // static item order only (layer-interleaved, ocean_fused.cuh); OCEAN_FUSED_1024 overrides for this size alone
+        static const int m1024 = [] { const char* e = getenv("OCEAN_FUSED_1024"); return e == nullptr ? -1 : (e[0] != '0'); }();
+        if (m1024 >= 0) return m1024;
+        return mode >= 0 ? (mode != 0) : OCEAN_FUSED_DEFAULT_1024;
+    }
     if (mode >= 0 && mode <= 2) return mode;
     return N == 256 ? OCEAN_FUSED_DEFAULT_256 : OCEAN_FUSED_DEFAULT_512;
 }
@@ -1175,6 +1189,7 @@ cudaError_t launch_frame(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream
     }
     if (a.N == 512) return frame_launch<512>(a, *maps, s, early);
     if (a.N == 256) return frame_launch<256>(a, *maps, s, early);
+    if (a.N == 1024) return frame_launch<1024>(a, *maps, s, early);
     return cudaErrorNotSupported;
 }
 

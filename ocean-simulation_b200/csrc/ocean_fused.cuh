@@ -53,21 +53,27 @@ struct FrameItem {
 #ifndef OCEAN_FUSED_ORDER
 #define OCEAN_FUSED_ORDER 0
 #endif
-__device__ __forceinline__ FrameItem frame_item(int pos, int ipl, int layers) {
+__device__ __forceinline__ FrameItem frame_item(int pos, int ipl, int layers, int order = OCEAN_FUSED_ORDER) {
     FrameItem it;
     const int g = pos / ipl;
     it.idx = pos - g * ipl;
-#if OCEAN_FUSED_ORDER == 0
-    it.role = g >= layers;
-    it.layer = g >= layers ? g - layers : g;
-#else
-    if (g == 0) { it.role = 0; it.layer = 0; }
-    else if (g == 2 * layers - 1) { it.role = 1; it.layer = layers - 1; }
-    else if (g & 1) { it.role = 0; it.layer = (g + 1) >> 1; }
-    else { it.role = 1; it.layer = (g >> 1) - 1; }
-#endif
+    if (order == 0) {
+        it.role = g >= layers;
+        it.layer = g >= layers ? g - layers : g;
+    } else if (layers == 1) {
+        it.role = g; it.layer = 0;
+    } else {
+        if (g == 0) { it.role = 0; it.layer = 0; }
+        else if (g == 2 * layers - 1) { it.role = 1; it.layer = layers - 1; }
+        else if (g & 1) { it.role = 0; it.layer = (g + 1) >> 1; }
+        else { it.role = 1; it.layer = (g >> 1) - 1; }
+    }
     return it;
 }
+// N = 1024: the row -> column workspace of all layers (134 MB at 4 x 1024^2) does not fit the 126 MB L2, so the items run in
+// the layer-interleaved order R0 R1 C0 R2 C1 ... : at most two layers' planes (67 MB) are live between their rows and
+// their columns, and a layer's columns read its rows while they are still L2-resident.
+template <int N> struct FusedOrder { static constexpr int value = N >= 1024 ? 1 : OCEAN_FUSED_ORDER; };
 
 template <int N>
 __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const FrameArgs& a, float4* bufA, float4* bufB, float4* bufT,
@@ -111,7 +117,7 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
     };
 
     int pos = blockIdx.x;
-    FrameItem cur = pos < totalItems ? frame_item(pos, Cfg::IPL, a.layers) : FrameItem{-1, 0, 0};
+    FrameItem cur = pos < totalItems ? frame_item(pos, Cfg::IPL, a.layers, FusedOrder<N>::value) : FrameItem{-1, 0, 0};
     if (cur.role >= 0) {
         if (cur.role == 1) spin_until_ge(a.rowsDone + cur.layer, a.rowsTarget);
         begin(cur);
@@ -119,7 +125,7 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
     uint32_t parity = 0;
     while (cur.role >= 0) {
         const int npos = pos + gridDim.x;
-        const FrameItem nxt = npos < totalItems ? frame_item(npos, Cfg::IPL, a.layers) : FrameItem{-1, 0, 0};
+        const FrameItem nxt = npos < totalItems ? frame_item(npos, Cfg::IPL, a.layers, FusedOrder<N>::value) : FrameItem{-1, 0, 0};
         // The next item's loads start as soon as a buffer is free AND the item is ready.  Readiness is
         // only polled here, never waited for, before this item has been published: blocking on the next
         // item's dependency could wait for a signal this very CTA still has to send.
@@ -184,7 +190,7 @@ __device__ __forceinline__ void fused_producer(const ColsTmaMaps& maps, const Fr
 // (evolve_texel: ocean_frame.cu)
 
 template <int N>
-__global__ void __launch_bounds__(FusedCfg<N>::THREADS, 2)
+__global__ void __launch_bounds__(FusedCfg<N>::THREADS, N >= 1024 ? 1 : 2)
 ocean_frame_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs a) {
     using Cfg = FusedCfg<N>;
     using ColFFT = typename Cfg::ColFFT;
@@ -218,7 +224,7 @@ ocean_frame_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs a) 
     const bool zeroFoam = a.zeroFoam != 0;
     uint32_t parity = 0;
     for (int pos = blockIdx.x; pos < totalItems; pos += gridDim.x, parity ^= 1) {
-        const FrameItem it = frame_item(pos, Cfg::IPL, a.layers);
+        const FrameItem it = frame_item(pos, Cfg::IPL, a.layers, FusedOrder<N>::value);
         C2 r[8];
         TRACE(0, pos, 0);
 #ifdef OCEAN_TRACE

@@ -246,6 +246,15 @@ static size_t l2_set_aside(int device) {
     cache[device] = bytes;
     return (size_t)bytes;
 }
+// How many layers' workspace planes (N*N*32 B each) the frame asks L2 to keep (evict_last stores); the others are streamed
+// (evict_first stores, read-once loads).  Default: all of them, also where they cannot all fit (4 x 1024^2: 134 MB of planes
+// against 126 MB of L2) -- measured on B200, us per 4 x 1024^2 frame with 4 / 3 / 2 / 1 / 0 resident layers:
+// 126.5 / 127.6 / 128.3 / 128.2 / 131.2 (profiles/r2_experiments.txt): partial residency buys nothing.  OCEAN_WS_RESIDENT=k forces k.
+static int ws_resident_layers(int /*device*/, int /*N*/, int layers) {
+    static const int forced = [] { const char* e = getenv("OCEAN_WS_RESIDENT"); return e ? atoi(e) : -1; }();
+    if (forced >= 0) return forced < layers ? forced : layers;
+    return layers;
+}
 static void l2_window(int device, const Workspace* w, FrameArgs* a) {
     a->l2Window = nullptr; a->l2WindowBytes = 0; a->l2HitRatio = 0.0f;
     const size_t aside = l2_set_aside(device);
@@ -344,6 +353,7 @@ struct OceanHandle {
     float2* waveHot = nullptr;  // (1/|k|, omega): compact copy of waveData read by the frame kernels
     float2* h0c = nullptr;      // h0(k): compact copy of h0.xy read by the pair-row kernel
     ColsTmaMaps colsMaps;       // TMA descriptors over rowsA / rowsB and the outputs
+    int wsResident = 0;         // layers whose workspace planes stay L2-resident (ws_resident_layers)
     bool rowsPending = false;   // ocean_step_partial: a row pass was issued and its column pass has not been
     float2* twiddle = nullptr;
     StateConsts* stateDev = nullptr;
@@ -419,6 +429,7 @@ int OceanHandle::AttachWorkspace(cudaStream_t shared) {
     rowsA = w->planeA();
     rowsB = w->planeB();
     l2_window(device, ws, &l2);
+    wsResident = ws_resident_layers(device, N, C);
     OCEAN_CUDA(make_cols_maps(N, C, rowsA, rowsB, disp, deriv, turb, &colsMaps));
     return OCEAN_OK;
 }
@@ -499,6 +510,7 @@ int OceanHandle::CalculateWavesTexturesAtTime(float time, int which, float* heig
     a.auxTarget = auxSignals;
     a.heightOut = heightOut;
     a.gravity = params.gravity;
+    a.wsResident = wsResident;
     const int fusedMode = which == 0 && !auxSignals ? frame_fused_mode(N, &colsMaps) : 0;
     if (fusedMode) {
         if (fusedMode == 2) workspace_stamp_queue(ws, 2 * C * (N / 4), frame_fused_grid(N, C, 2), &a);
@@ -976,6 +988,7 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         fa.lambda = states[base].lambda;  // one lambda per wave: the frame kernels take it as a scalar
         fa.foamDecay = expf(-2.0f);
         fa.zeroFoam = 1;
+        fa.wsResident = fa.layers;  // (ensemble waves keep round 1's policy: every plane evict_last)
         // a short last wave leaves the upper layers' counters behind: restart the counting per wave
         L.ws->rowPasses = L.ws->colPasses = 0;
         L.ws->queueFrames = 0; L.ws->queueNext[0] = L.ws->queueNext[1] = 0;

@@ -101,6 +101,9 @@ struct FrameArgs {
     // (= layer / C) when `states` is set (ensembles), else the scalar.
     const StateConsts* states;
     float gravity;
+    // Layers [0, wsResident) keep their workspace planes L2-resident (evict_last stores); the others are streamed
+    // (evict_first stores, read-once loads).  = layers when everything fits (the usual case).
+    int wsResident;
     // L2 residency of the intermediate planes (host-side launch attribute, not read by the kernels):
     // accesses inside [l2Window, +l2WindowBytes) are marked persisting with this hit ratio.
     const void* l2Window;

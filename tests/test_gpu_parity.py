@@ -658,3 +658,22 @@ def test_default_ensemble_path_at_config5_size_matches_oracle(pkg, po):
         ob.close()
     ens.close()
     whole.close()
+
+
+def test_config4_opt_in_paths_match_the_default(pkg, po):
+    """4 x 1024^2 through the two opt-in paths of round 2 -- the fused frame kernel with the layer-interleaved item order
+    (OCEAN_FUSED_1024=1) and partial workspace residency (OCEAN_WS_RESIDENT=2) -- in child processes (the switches are read
+    once): the digests of all three output arrays after three frames equal the default path's, bit for bit."""
+    import json, os, subprocess, sys
+    child = (
+        "import os, sys, hashlib; sys.path.insert(0, %r); import oceanpkg; pkg = oceanpkg.load(); cfg = pkg.scene.config(4); o = cfg['ocean']\n"
+        "b = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5], texturesSize=cfg['N'], cascades=cfg['cascades'], seed=4).Awake()\n"
+        "[b.CalculateWavesTexturesAtTime(f / 60.0) for f in range(3)]\n"
+        "h = hashlib.sha256(); [h.update(a.tobytes()) for a in (b.displacementsTextures, b.derivativesTextures, b.turbulenceTextures)]; print(h.hexdigest())\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = {}
+    for name, env in (("default", {}), ("fused", {"OCEAN_FUSED_1024": "1"}), ("resident2", {"OCEAN_WS_RESIDENT": "2"})):
+        r = subprocess.run([sys.executable, "-c", child], env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-1500:]
+        digests[name] = r.stdout.strip().splitlines()[-1]
+    assert digests["fused"] == digests["default"] and digests["resident2"] == digests["default"], digests

@@ -33,10 +33,11 @@ for rep in range(3):
 print(json.dumps({"frame_us": round(1e3 * best, 3), "digest": h.hexdigest()[:12], "finite": bool(np.isfinite(bodies[0].turbulenceTextures).all())}))
 ''' % ROOT
 args = [a for a in sys.argv[1:] if not a.startswith("--")]
-cfgno = 2 if "--n256" in sys.argv else 3
+for flag in ("--frames", "--cfg"):
+    if flag in sys.argv: args.remove(sys.argv[sys.argv.index(flag) + 1])
+cfgno = 2 if "--n256" in sys.argv else (int(sys.argv[sys.argv.index("--cfg") + 1]) if "--cfg" in sys.argv else 3)
 K = int(sys.argv[sys.argv.index("--frames") + 1]) if "--frames" in sys.argv else 400
 for spec in args:
-    if spec.isdigit(): continue
     name, lib, envs = (spec.split(":") + ["", ""])[:3]
     env = dict(os.environ)
     if lib: env["OCEANFFT_LIB"] = lib if os.path.isabs(lib) else os.path.join(ROOT, lib)
