@@ -636,6 +636,9 @@ __global__ void __launch_bounds__(ColCfg<N>::THREADS, ColCfg<N>::MINB) ocean_col
 #ifndef OCEAN_COLS_EARLY_PRODUCER
 #define OCEAN_COLS_EARLY_PRODUCER 0  // 1: an isolated column pass starts 1.1 us sooner, back-to-back frames are 0.2 us slower
 #endif
+#ifndef OCEAN_COLS_TW_SMEM
+#define OCEAN_COLS_TW_SMEM 1  // 0: the column pass reads its twiddles through the read-only path (7 KB less shared memory per CTA at N = 512)
+#endif
 #ifndef OCEAN_COLS_REVERSE_LAYERS
 #define OCEAN_COLS_REVERSE_LAYERS 0
 #endif
@@ -652,8 +655,8 @@ template <int N> struct ColTmaCfg {
     static constexpr int BOX_ROWS = N < 256 ? N : 256;
     static constexpr int NBOX = N / BOX_ROWS;
     static constexpr int TILE_ELEMS = N * W;                    // 128-bit elements per tile plane
-    using FFT = LineFFT<N, W, true, false, true, true, COMPUTE>;
-    static constexpr int TW_BYTES = FFT::TWIDDLE_ENTRIES * 8;
+    using FFT = LineFFT<N, W, true, false, true, OCEAN_COLS_TW_SMEM != 0, COMPUTE>;
+    static constexpr int TW_BYTES = OCEAN_COLS_TW_SMEM ? FFT::TWIDDLE_ENTRIES * 8 : 0;
     static constexpr int SMEM_BYTES = 3 * TILE_ELEMS * 16 + TW_BYTES + 64;  // A, B, turbulence staging, twiddles, mbarriers
 };
 
@@ -675,8 +678,9 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     float4* bufA = smem;
     float4* bufB = smem + Cfg::TILE_ELEMS;
     float4* bufT = smem + 2 * Cfg::TILE_ELEMS;
-    float2* twS = (float2*)(smem + 3 * Cfg::TILE_ELEMS);
-    uint64_t* bars = (uint64_t*)((char*)twS + Cfg::TW_BYTES);  // [0] full A, [1] full B, [2] staged A, [3] staged B
+    float2* twSmem = (float2*)(smem + 3 * Cfg::TILE_ELEMS);
+    const float2* twS = OCEAN_COLS_TW_SMEM ? twSmem : a.twiddle;  // the table the transforms read
+    uint64_t* bars = (uint64_t*)((char*)twSmem + Cfg::TW_BYTES);  // [0] full A, [1] full B, [2] staged A, [3] staged B
     __shared__ unsigned long long ckPart[CK ? (Cfg::COMPUTE / 32) * 3 : 1];  // per-warp (disp, deriv, turb) sums of a tile
 
     pdl_trigger();
@@ -694,7 +698,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
     }
     __syncthreads();
     if (threadIdx.x < Cfg::COMPUTE) {
-        for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::COMPUTE) twS[i] = __ldg(&a.twiddle[i]);
+        if (OCEAN_COLS_TW_SMEM) for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::COMPUTE) twSmem[i] = __ldg(&a.twiddle[i]);
         FFT::barrier();
     }
 #else
@@ -706,7 +710,7 @@ ocean_cols_tma_kernel(const __grid_constant__ ColsTmaMaps maps, const FrameArgs 
         mbar_fence_init();
     }
     // the twiddle table is immutable: copying it may overlap the previous kernel
-    for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twS[i] = __ldg(&a.twiddle[i]);
+    if (OCEAN_COLS_TW_SMEM) for (int i = threadIdx.x; i < FFT::TWIDDLE_ENTRIES; i += Cfg::THREADS) twSmem[i] = __ldg(&a.twiddle[i]);
     __syncthreads();
 #endif
     // No griddepcontrol.wait here, and none in the row kernels either: the producer gates every tile on its

@@ -30,6 +30,9 @@ VARIANTS = {
     "hetero_g5": ["-DOCEAN_HETERO_G=5"],
     "hetero_g6": ["-DOCEAN_HETERO_G=6"],
     "hetero_g7": ["-DOCEAN_HETERO_G=7"],
+    "rows_m16": ["-DOCEAN_ROWS512_MINB=16"],
+    "cols_tw_global": ["-DOCEAN_COLS_TW_SMEM=0"],
+    "rows_m16_cols_tw_global": ["-DOCEAN_ROWS512_MINB=16", "-DOCEAN_COLS_TW_SMEM=0"],
     "rows_recompute_hot": ["-DOCEAN_ROWS_RECOMPUTE_HOT=1"],
     "cols_reverse_1024": ["-DOCEAN_COLS_REVERSE_LAYERS=1"],
 }
