@@ -286,13 +286,22 @@ def run_cuda(args):
     bx[:, 3:] = rng.uniform(0.5, 2.0, (BOXES, 3))
     h_boxes[:] = torch.from_numpy(bx)
 
+    # per-step host work is the C-ABI call alone (what a C# caller pays): handles and buffer addresses are looked up once
+    import ctypes
+    handles = [b._h for b in bodies]
+    box_ptr = [[ctypes.c_void_p(h_boxes[i, r].data_ptr()) for r in range(RING)] for i in range(INSTANCES)]
+    out_ptr = [[ctypes.c_void_p(h_out[i, r].data_ptr()) for r in range(RING)] for i in range(INSTANCES)]
+    update_buoyancy, update = lib.ocean_update_buoyancy, lib.ocean_update
+
     def e2e_step(mode):
         f, t = tick()
         i, r = f % INSTANCES, (f // INSTANCES) % RING
         if mode == "query":
-            bodies[i].UpdateBuoyancy(t, (h_boxes[i, r].data_ptr(), BOXES), (h_out[i, r].data_ptr(),), density=1.0, gravityY=-9.81)
+            rc = update_buoyancy(handles[i], t, box_ptr[i][r], BOXES, 1.0, -9.81, out_ptr[i][r])
         else:
-            bodies[i].Update(t)
+            rc = update(handles[i], t)
+        if rc != 0:
+            L.check(rc)
 
     def run_e2e(mode):
         if mode != "query":
