@@ -50,11 +50,19 @@ OCEAN_HD uint64_t ocean_mix64(uint64_t z) {
     return z;
 }
 
-/* Uniform in [0,1) with 24 random bits, keyed on (seed, draw counter, rejection attempt, lane). */
-OCEAN_HD float ocean_uniform(uint64_t seed, uint64_t counter, uint32_t attempt, uint32_t lane) {
-    uint64_t z = ocean_mix64(seed + 0x9E3779B97F4A7C15ull * (counter + 1));
-    z = ocean_mix64(z ^ (((uint64_t)attempt << 1 | lane) * 0xD6E8FEB86659FD93ull + 0x2545F4914F6CDD1Dull));
+/* Uniform in [0,1) with 24 random bits, keyed on (seed, draw counter, rejection attempt, lane).  The first mixing round
+ * depends on (seed, counter) only: ocean_counter_key() evaluates it once per draw and the rejection loop of ocean_gaussian
+ * re-uses it for every attempt and both lanes (same bits as hashing it again each time, a third fewer integer multiplies --
+ * on the GPU a warp runs the loop until its slowest lane accepts, ~3 iterations per normal). */
+OCEAN_HD uint64_t ocean_counter_key(uint64_t seed, uint64_t counter) {
+    return ocean_mix64(seed + 0x9E3779B97F4A7C15ull * (counter + 1));
+}
+OCEAN_HD float ocean_uniform_keyed(uint64_t key, uint32_t attempt, uint32_t lane) {
+    const uint64_t z = ocean_mix64(key ^ (((uint64_t)attempt << 1 | lane) * 0xD6E8FEB86659FD93ull + 0x2545F4914F6CDD1Dull));
     return (float)(uint32_t)(z >> 40) * 5.9604644775390625e-8f; /* 2^-24, exact */
+}
+OCEAN_HD float ocean_uniform(uint64_t seed, uint64_t counter, uint32_t attempt, uint32_t lane) {
+    return ocean_uniform_keyed(ocean_counter_key(seed, counter), attempt, lane);
 }
 
 OCEAN_HD uint32_t ocean_f2u(float f) { union { float f; uint32_t u; } c; c.f = f; return c.u; }
@@ -88,9 +96,10 @@ OCEAN_HD float ocean_logf(float x) {
 OCEAN_HD float ocean_gaussian(uint64_t seed, uint64_t counter) {
     float v1, s;
     uint32_t attempt = 0;
+    const uint64_t key = ocean_counter_key(seed, counter);
     for (;;) {
-        v1 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform(seed, counter, attempt, 0u)), 1.0f);
-        float v2 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform(seed, counter, attempt, 1u)), 1.0f);
+        v1 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 0u)), 1.0f);
+        float v2 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 1u)), 1.0f);
         s = OCEAN_FMA(v1, v1, OCEAN_FMUL(v2, v2));
         ++attempt;
         if (!(s >= 1.0f || s == 0.0f)) break;

@@ -866,6 +866,9 @@ void OceanHandle::OnDisable() {
 // -> row pass -> column pass (memory-bound).  Each lane owns a stream and a full set of pooled buffers;
 // consecutive waves alternate between the lanes, so the ALU-bound kernels of one wave share the SMs with
 // the memory-bound kernels of the other instead of running after them (OCEAN_ENSEMBLE_LANES=1: one lane).
+#ifndef OCEAN_ENSEMBLE_ALU_CTAS_PER_SM_DEFAULT
+#define OCEAN_ENSEMBLE_ALU_CTAS_PER_SM_DEFAULT 0
+#endif
 struct EnsembleLane {
     cudaStream_t stream = nullptr;
     float2* noise = nullptr;
@@ -892,6 +895,8 @@ struct OceanEnsemble {
     // N4); h0 / waveHot are never materialised (40 B per texel-cascade less pooled memory).  Off by default: the
     // spectrum is ALU-bound and the separate kernels are ~9 % faster on B200 (ocean_init.cu).
     bool fusedInit = false;
+    // grid cap of the ALU-bound noise / spectrum kernels (OCEAN_ENSEMBLE_ALU_CTAS_PER_SM x SMs; 0 = one CTA per work item)
+    int aluCtas = 0;
     OceanCascade cascades[OCEAN_MAX_CASCADES]{};
     EnsembleLane lane[MAX_LANES];
     float2* twiddle = nullptr;
@@ -908,6 +913,12 @@ int OceanEnsemble::create() {
     const size_t t = (size_t)N * N;
     if (const char* e = getenv("OCEAN_ENSEMBLE_LANES")) lanes = atoi(e) <= 1 ? 1 : MAX_LANES;
     if (const char* e = getenv("OCEAN_ENSEMBLE_FUSED_INIT")) fusedInit = rows_from_noise_available(N) && atoi(e) != 0;
+    {
+        int perSM = OCEAN_ENSEMBLE_ALU_CTAS_PER_SM_DEFAULT, sms = 0;
+        if (const char* e = getenv("OCEAN_ENSEMBLE_ALU_CTAS_PER_SM")) perSM = atoi(e);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        aluCtas = (lanes > 1 && perSM > 0 && sms > 0) ? perSM * sms : 0;
+    }
     const std::vector<float2> tw = make_twiddles(N);
     OCEAN_CUDA(cudaMalloc(&twiddle, tw.size() * sizeof(float2)));
     OCEAN_CUDA(cudaMemcpy(twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
@@ -974,11 +985,11 @@ int OceanEnsemble::run(const OceanParams* states, const uint64_t* seeds, int nSt
         OCEAN_CUDA(cudaMemcpyAsync(L.stateDev, L.stateHost, nb * sizeof(StateConsts), cudaMemcpyHostToDevice, stream));
         OCEAN_CUDA(cudaMemcpyAsync(L.seedDev, L.seedHost, nb * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
         OCEAN_CUDA(cudaMemsetAsync(L.sumDev, 0, (size_t)nb * 3 * sizeof(unsigned long long), stream));
-        OCEAN_CUDA(launch_noise(L.seedDev, nb, N, L.noise, stream));
+        OCEAN_CUDA(launch_noise(L.seedDev, nb, N, L.noise, stream, aluCtas));
         // waveData (the reference's inspection layout) is not kept by ensembles: the frame reads waveHot
         ia.noise = L.noise; ia.h0 = L.h0; ia.wave = nullptr; ia.waveHot = L.waveHot; ia.h0c = L.h0c;
         ia.nStates = nb; ia.states = L.stateDev;
-        if (!fusedInit) OCEAN_CUDA(launch_init(ia, stream));
+        if (!fusedInit) OCEAN_CUDA(launch_init(ia, stream, aluCtas));
         FrameArgs fa{};
         fa.N = N; fa.layers = nb * C; fa.C = C;
         for (int i = 0; i < C; ++i) fa.dk[i] = ia.casc[i].dk;

@@ -17,10 +17,7 @@
 
 namespace ocean {
 
-__global__ void ocean_noise_kernel(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y;
-    const int st = blockIdx.z;
+__device__ __forceinline__ void noise_texel_pair(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise, int x, int y, int st) {
     if (x >= N) return;
     const uint64_t seed = seeds[st];
     float2 v;
@@ -28,16 +25,28 @@ __global__ void ocean_noise_kernel(const uint64_t* __restrict__ seeds, int N, fl
     v.y = ocean_noise_texel(seed, (uint32_t)N, (uint32_t)x, (uint32_t)y, 1u);
     noise[((size_t)st * N + y) * N + x] = v;
 }
+__global__ void ocean_noise_kernel(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise) {
+    noise_texel_pair(seeds, N, noise, blockIdx.x * blockDim.x + threadIdx.x, blockIdx.y, blockIdx.z);
+}
+// Ensembles: the same work items (gx x gy x gz CTAs' worth) walked by a grid that occupies only part of every SM, so that the
+// memory-bound frame kernels of the OTHER lane find thread slots and registers beside this ALU-bound kernel instead of
+// only at its tail (OceanEnsemble, OCEAN_ENSEMBLE_ALU_CTAS_PER_SM).  Same arithmetic per item: bit-identical results.
+__global__ void __launch_bounds__(128) ocean_noise_persistent_kernel(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise,
+                                                                     int gx, int gy, int gz) {
+    const long long total = (long long)gx * gy * gz;
+    for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+        const int bx = (int)(w % gx), by = (int)((w / gx) % gy), bz = (int)(w / ((long long)gx * gy));
+        noise_texel_pair(seeds, N, noise, bx * blockDim.x + threadIdx.x, by, bz);
+    }
+}
 
-__global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs a) {
+__device__ __forceinline__ void init_texel_pair(const InitArgs& a, const int x, const int y /* 0 .. N/2 */, const int layerIdx) {
     const int N = a.N;
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y;  // 0 .. N/2
     if (x >= N) return;
     const int mx = (N - x) & (N - 1), my = (N - y) & (N - 1);  // IS:139
     // rows 0 and N/2 mirror onto themselves: the pair {x, mx} is handled by the thread with x <= mx
     if (my == y && x > mx) return;
-    const int layer = blockIdx.z;
+    const int layer = layerIdx;
     const int st = layer / a.C, ci = layer - st * a.C;
     const StateConsts sc = a.states[st];
     const CascadeConsts cc = a.casc[ci];
@@ -68,6 +77,18 @@ __global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs
     if (a.h0c) {
         a.h0c[p] = tp.h;
         a.h0c[m] = tm.h;
+    }
+}
+
+__global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs a) {
+    init_texel_pair(a, blockIdx.x * blockDim.x + threadIdx.x, blockIdx.y, blockIdx.z);
+}
+// (see ocean_noise_persistent_kernel)
+__global__ void __launch_bounds__(128) ocean_init_spectrum_persistent_kernel(const InitArgs a, int gx, int gy, int gz) {
+    const long long total = (long long)gx * gy * gz;
+    for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+        const int bx = (int)(w % gx), by = (int)((w / gx) % gy), bz = (int)(w / ((long long)gx * gy));
+        init_texel_pair(a, bx * blockDim.x + threadIdx.x, by, bz);
     }
 }
 
@@ -217,16 +238,20 @@ cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaS
     }
 }
 
-cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s) {
+cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s, int maxCtas) {
     dim3 block(N < 128 ? N : 128), grid((N + block.x - 1) / block.x, N, nStates);
-    ocean_noise_kernel<<<grid, block, 0, s>>>(seedsDev, N, noise);
+    const long long total = (long long)grid.x * grid.y * grid.z;
+    if (maxCtas > 0 && total > maxCtas) ocean_noise_persistent_kernel<<<maxCtas, block, 0, s>>>(seedsDev, N, noise, (int)grid.x, (int)grid.y, (int)grid.z);
+    else ocean_noise_kernel<<<grid, block, 0, s>>>(seedsDev, N, noise);
     count_launch();
     return cudaGetLastError();
 }
 
-cudaError_t launch_init(const InitArgs& a, cudaStream_t s) {
+cudaError_t launch_init(const InitArgs& a, cudaStream_t s, int maxCtas) {
     dim3 block(a.N < 128 ? a.N : 128), grid((a.N + block.x - 1) / block.x, a.N / 2 + 1, a.nStates * a.C);
-    ocean_init_spectrum_kernel<<<grid, block, 0, s>>>(a);
+    const long long total = (long long)grid.x * grid.y * grid.z;
+    if (maxCtas > 0 && total > maxCtas) ocean_init_spectrum_persistent_kernel<<<maxCtas, block, 0, s>>>(a, (int)grid.x, (int)grid.y, (int)grid.z);
+    else ocean_init_spectrum_kernel<<<grid, block, 0, s>>>(a);
     count_launch();
     return cudaGetLastError();
 }

@@ -124,8 +124,10 @@ cudaError_t make_cols_maps(int N, int layers, const float4* rowsA, const float4*
                            ColsTmaMaps* out);
 
 // launchers (return cudaGetLastError()); every launch bumps the launch counter
-cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s);
-cudaError_t launch_init(const InitArgs& a, cudaStream_t s);
+// maxCtas > 0: walk the same work items with a persistent grid of at most maxCtas CTAs (ensembles: leaves room on every SM
+// for the other lane's frame kernels); 0: one CTA per item
+cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s, int maxCtas = 0);
+cudaError_t launch_init(const InitArgs& a, cudaStream_t s, int maxCtas = 0);
 // Initial spectrum fused into the row pass: noise -> h0 (shared memory only) -> evolution -> x-FFT
 // -> workspace planes, for oceans that are evolved once from a fresh spectrum.  InitArgs::h0 / wave / waveHot are
 // not written.  The static `configured` flag is per process and per size: call with the target device current.
