@@ -92,20 +92,26 @@ OCEAN_HD float ocean_logf(float x) {
     return OCEAN_FSUB(OCEAN_FMUL(dk, ln2_hi), OCEAN_FSUB(OCEAN_FSUB(hfsq, inner), f));
 }
 
+/* One attempt of the WB:71-81 rejection loop for the draw keyed by `key`: (v1, s) and whether it is accepted (WB:77). */
+OCEAN_HD int ocean_gaussian_attempt(uint64_t key, uint32_t attempt, float* v1, float* s) {
+    *v1 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 0u)), 1.0f);
+    const float v2 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 1u)), 1.0f);
+    *s = OCEAN_FMA(*v1, *v1, OCEAN_FMUL(v2, v2));
+    return !(*s >= 1.0f || *s == 0.0f);
+}
+/* ... and the transform of an accepted pair (WB:79-80). */
+OCEAN_HD float ocean_gaussian_finish(float v1, float s) {
+    s = OCEAN_FSQRT(OCEAN_FDIV(OCEAN_FMUL(-2.0f, ocean_logf(s)), s));
+    return OCEAN_FMUL(v1, s);
+}
+
 /* One N(0,1) draw: the WB:71-81 rejection loop on the counter-based uniforms. */
 OCEAN_HD float ocean_gaussian(uint64_t seed, uint64_t counter) {
     float v1, s;
     uint32_t attempt = 0;
     const uint64_t key = ocean_counter_key(seed, counter);
-    for (;;) {
-        v1 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 0u)), 1.0f);
-        float v2 = OCEAN_FSUB(OCEAN_FMUL(2.0f, ocean_uniform_keyed(key, attempt, 1u)), 1.0f);
-        s = OCEAN_FMA(v1, v1, OCEAN_FMUL(v2, v2));
-        ++attempt;
-        if (!(s >= 1.0f || s == 0.0f)) break;
-    }
-    s = OCEAN_FSQRT(OCEAN_FDIV(OCEAN_FMUL(-2.0f, ocean_logf(s)), s));
-    return OCEAN_FMUL(v1, s);
+    while (!ocean_gaussian_attempt(key, attempt, &v1, &s)) ++attempt;
+    return ocean_gaussian_finish(v1, s);
 }
 
 /*

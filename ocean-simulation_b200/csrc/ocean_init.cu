@@ -9,6 +9,8 @@
 // Each thread owns the texel pair {p, mirror(p)} with mirror(x, y) = ((N-x)%N, (N-y)%N): it
 // evaluates h0 once at each texel and writes both (h0(p), conj h0(m)) and (h0(m), conj h0(p)),
 // so the amplitude is never computed twice and the reference's in-place second pass disappears.
+#include <stdlib.h>
+
 #include "ocean_internal.h"
 #include "../../include/ocean_noise.h"
 #include "ocean_spectrum.cuh"
@@ -25,6 +27,49 @@ __device__ __forceinline__ void noise_texel_pair(const uint64_t* __restrict__ se
     v.y = ocean_noise_texel(seed, (uint32_t)N, (uint32_t)x, (uint32_t)y, 1u);
     noise[((size_t)st * N + y) * N + x] = v;
 }
+// The noise texture with the rejection loop load-balanced inside a thread.  With one draw per loop a warp iterates until its
+// SLOWEST lane accepts: ~3 iterations per normal against 1.27 per lane (ncu: 592 instructions per texel, issue-bound).  Here a
+// thread owns DRAWS = 8 draws -- 4 adjacent texels x (r, g) -- and runs ONE loop over all of them, moving on to its next draw
+// the moment one is accepted; a warp then iterates for the slowest lane's SUM of attempts (~14 for 8 draws instead of ~24).
+// Accepted (v1, s) pairs are parked in shared memory and transformed after the loop, outside the divergent part.  Attempt test
+// and transform are the header's own functions (include/ocean_noise.h): the bits are those of ocean_noise_texel.
+constexpr int kNoiseDraws = 8, kNoiseThreads = 128;
+__global__ void __launch_bounds__(kNoiseThreads) ocean_noise_balanced_kernel(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise,
+                                                                             long long groups) {
+    __shared__ float2 parked[kNoiseDraws][kNoiseThreads];
+    const long long gid = (long long)blockIdx.x * kNoiseThreads + threadIdx.x;
+    if (gid >= groups) return;
+    const int gpr = N / 4;  // groups of 4 texels per row
+    const int xg = (int)(gid % gpr), y = (int)((gid / gpr) % N), st = (int)(gid / ((long long)gpr * N));
+    const uint64_t seed = seeds[st];
+    const uint32_t x0 = (uint32_t)xg * 4u;
+    // draw d: texel x0 + d / 2, channel d & 1; counter = (x * N + y) * 2 + ch  (ocean_noise_texel)
+    auto counter = [&](int d) { return ((uint64_t)(x0 + (uint32_t)(d >> 1)) * (uint32_t)N + (uint32_t)y) * 2u + (uint32_t)(d & 1); };
+    int d = 0;
+    uint32_t attempt = 0;
+    uint64_t key = ocean_counter_key(seed, counter(0));
+    while (d < kNoiseDraws) {
+        float v1, s;
+        if (ocean_gaussian_attempt(key, attempt, &v1, &s)) {
+            parked[d][threadIdx.x] = make_float2(v1, s);
+            ++d;
+            attempt = 0;
+            key = ocean_counter_key(seed, counter(d));  // (d == 8: computed and never used)
+        } else {
+            ++attempt;
+        }
+    }
+    float out[kNoiseDraws];
+#pragma unroll
+    for (int i = 0; i < kNoiseDraws; ++i) {
+        const float2 p = parked[i][threadIdx.x];  // written by this thread only: no barrier
+        out[i] = ocean_gaussian_finish(p.x, p.y);
+    }
+    float4* dst = reinterpret_cast<float4*>(noise + ((size_t)st * N + y) * N + x0);  // 4 texels = 32 B, 32-byte aligned
+    dst[0] = make_float4(out[0], out[1], out[2], out[3]);
+    dst[1] = make_float4(out[4], out[5], out[6], out[7]);
+}
+
 __global__ void ocean_noise_kernel(const uint64_t* __restrict__ seeds, int N, float2* __restrict__ noise) {
     noise_texel_pair(seeds, N, noise, blockIdx.x * blockDim.x + threadIdx.x, blockIdx.y, blockIdx.z);
 }
@@ -241,8 +286,12 @@ cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaS
 cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* noise, cudaStream_t s, int maxCtas) {
     dim3 block(N < 128 ? N : 128), grid((N + block.x - 1) / block.x, N, nStates);
     const long long total = (long long)grid.x * grid.y * grid.z;
+    static const bool balanced = [] { const char* e = getenv("OCEAN_NOISE_BALANCED"); return e == nullptr || e[0] != '0'; }();
     if (maxCtas > 0 && total > maxCtas) ocean_noise_persistent_kernel<<<maxCtas, block, 0, s>>>(seedsDev, N, noise, (int)grid.x, (int)grid.y, (int)grid.z);
-    else ocean_noise_kernel<<<grid, block, 0, s>>>(seedsDev, N, noise);
+    else if (balanced) {
+        const long long groups = (long long)nStates * N * (N / 4);
+        ocean_noise_balanced_kernel<<<(unsigned)((groups + kNoiseThreads - 1) / kNoiseThreads), kNoiseThreads, 0, s>>>(seedsDev, N, noise, groups);
+    } else ocean_noise_kernel<<<grid, block, 0, s>>>(seedsDev, N, noise);
     count_launch();
     return cudaGetLastError();
 }
