@@ -158,3 +158,23 @@ def test_update_buoyancy_answers_on_the_owning_gpu(pkg, po, N):
     assert frame == frame0 and np.array_equal(layer, layer0)
     body.OnDisable()
     twin.OnDisable()
+
+
+def test_both_device_noise_kernels_equal_the_host_generator(pkg, po):
+    """The default noise kernel balances the WB:71-81 rejection loop over 8 draws per thread; OCEAN_NOISE_BALANCED=0 selects the
+    one-draw-per-loop kernel.  Both must reproduce include/ocean_noise.h on the host bit for bit (child processes: the switch is
+    read once), at a size with a single group per row block (16), a ragged last block (64 * 64 / 4 groups) and the headline size."""
+    import hashlib, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    child = (
+        "import sys, hashlib; sys.path.insert(0, %r); import oceanpkg; pkg = oceanpkg.load()\n"
+        "for N, seed in ((16, 5), (64, 1), (512, 12345678901234)):\n"
+        "    b = pkg.WaterBody(windSpeed=8, windDirection=(1, -1), fetch=50000, depth=2560, texturesSize=N, cascades=pkg.scene.SCENE_CASCADES[:1], seed=seed).Awake()\n"
+        "    print(N, hashlib.sha256(b.randomNoiseTexture.tobytes()).hexdigest()); b.OnDisable()\n"
+    ) % root
+    want = {N: hashlib.sha256(po.fill_noise(seed, N).tobytes()).hexdigest() for N, seed in ((16, 5), (64, 1), (512, 12345678901234))}
+    for env in ({}, {"OCEAN_NOISE_BALANCED": "0"}):
+        r = subprocess.run([sys.executable, "-c", child], env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-1500:]
+        got = {int(l.split()[0]): l.split()[1] for l in r.stdout.strip().splitlines()}
+        assert got == want, (env, got, want)
