@@ -125,7 +125,10 @@ __device__ __forceinline__ void init_texel_pair(const InitArgs& a, const int x, 
     }
 }
 
-__global__ void __launch_bounds__(128) ocean_init_spectrum_kernel(const InitArgs a) {
+#ifndef OCEAN_INIT_MINB
+#define OCEAN_INIT_MINB 1
+#endif
+__global__ void __launch_bounds__(128, OCEAN_INIT_MINB) ocean_init_spectrum_kernel(const InitArgs a) {
     init_texel_pair(a, blockIdx.x * blockDim.x + threadIdx.x, blockIdx.y, blockIdx.z);
 }
 // (see ocean_noise_persistent_kernel)
