@@ -1094,12 +1094,12 @@ template <int N> static cudaError_t configure_tma() {
 }
 template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsTmaMaps& m, cudaStream_t s, bool early) {
     using Cfg = FusedCfg<N>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.need()) {
         cudaError_t e = cudaFuncSetAttribute(ocean_frame_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         cudaFuncSetAttribute(ocean_frame_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        configured = true;
+        configured.mark();
     }
     static int ctasPerSM = 0;
     if (ctasPerSM == 0) {
@@ -1114,10 +1114,14 @@ template <int N> static cudaError_t frame_launch(const FrameArgs& a, const ColsT
 }
 template <int N> static int frame2_ctas_per_sm() {
     using Cfg = Fused2Cfg<N>;
-    static int ctasPerSM = 0;
-    if (ctasPerSM == 0) {
+    static PerDeviceOnce configured;
+    if (configured.need()) {
         cudaFuncSetAttribute(ocean_frame2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         cudaFuncSetAttribute(ocean_frame2_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured.mark();
+    }
+    static int ctasPerSM = 0;
+    if (ctasPerSM == 0) {
         int n = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ocean_frame2_kernel<N>, Cfg::THREADS, Cfg::SMEM_BYTES);
         ctasPerSM = n > 0 ? n : 1;
@@ -1140,13 +1144,13 @@ int hetero_mode(int N, const ColsTmaMaps* maps) {
     return (N == 512 && maps && maps->valid) ? mode : 0;
 }
 cudaError_t launch_hetero(const FrameArgs& a, const ColsTmaMaps* maps, cudaStream_t s, int mode) {
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.need()) {
         cudaError_t e = cudaFuncSetAttribute(ocean_hetero_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, HeteroCfg::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(ocean_hetero_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, HeteroCfg::SMEM_BYTES);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured.mark();
     }
     const int totalTiles = a.layers * (HeteroCfg::N / HeteroCfg::W);
     const int grid = num_sms();

@@ -263,12 +263,12 @@ bool rows_from_noise_available(int N) { return N == 128 || N == 256 || N == 512 
 
 template <int N> static cudaError_t rows_from_noise_launch(const InitArgs& ia, const FrameArgs& a, cudaStream_t s) {
     using Cfg = RowsFromNoiseCfg<N>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.need()) {
         cudaError_t e = cudaFuncSetAttribute(ocean_rows_from_noise_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         cudaFuncSetAttribute(ocean_rows_from_noise_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        configured = true;
+        configured.mark();
     }
     ocean_rows_from_noise_kernel<N><<<(unsigned)(a.layers * (N / 2)), Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(ia, a);
     count_launch();

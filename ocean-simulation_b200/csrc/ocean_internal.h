@@ -130,7 +130,7 @@ cudaError_t launch_noise(const uint64_t* seedsDev, int nStates, int N, float2* n
 cudaError_t launch_init(const InitArgs& a, cudaStream_t s, int maxCtas = 0);
 // Initial spectrum fused into the row pass: noise -> h0 (shared memory only) -> evolution -> x-FFT
 // -> workspace planes, for oceans that are evolved once from a fresh spectrum.  InitArgs::h0 / wave / waveHot are
-// not written.  The static `configured` flag is per process and per size: call with the target device current.
+// not written.  Call with the target device current (the kernel is configured once per device: PerDeviceOnce).
 bool rows_from_noise_available(int N);
 cudaError_t launch_rows_from_noise(const InitArgs& ia, const FrameArgs& a, cudaStream_t s);
 // early: the row pass may start before the previous kernel in the stream has finished (PDL).  Only
@@ -176,5 +176,16 @@ const char* describe_frame_kernels(int N);   // "rows<N,R> grid.. smem..; cols<N
 
 void count_launch();
 uint64_t launch_count();
+
+// "Configure this kernel once" flags.  cudaFuncSetAttribute (dynamic shared memory size, carve-out) applies to the CURRENT
+// DEVICE only, so a process that drives several GPUs must configure every kernel once per device: a process-wide static flag
+// makes the first launch on a second device fail with "invalid argument" (found by tests/test_zz_no_alloc.py on a 2-GPU box).
+struct PerDeviceOnce {
+    unsigned long long done = 0;  // bit d: configured on device d (the library's entry points serialise per handle; a benign
+                                  // race between threads on different devices can at worst configure a kernel twice)
+    static int current() { int d = 0; return cudaGetDevice(&d) == cudaSuccess ? d : -1; }
+    bool need() const { const int d = current(); return d < 0 || d >= 64 || !(done & (1ull << d)); }
+    void mark() { const int d = current(); if (d >= 0 && d < 64) done |= 1ull << d; }
+};
 
 }  // namespace ocean

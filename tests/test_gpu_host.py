@@ -178,3 +178,38 @@ def test_both_device_noise_kernels_equal_the_host_generator(pkg, po):
         assert r.returncode == 0, r.stderr[-1500:]
         got = {int(l.split()[0]): l.split()[1] for l in r.stdout.strip().splitlines()}
         assert got == want, (env, got, want)
+
+
+def test_two_devices_in_one_process(pkg, po):
+    """cudaFuncSetAttribute is per device: every frame path must configure its kernels on each GPU it runs on.  Oceans on cuda:1
+    (created first) and cuda:0 in ONE process, at the sizes that select the fused frame kernel (256) and the two-kernel frame
+    (512), plus an ensemble with the spectrum fused into the row pass: same bits on both GPUs.  Skipped on one GPU."""
+    lib = pkg._lib.load()
+    if lib.ocean_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cfg = pkg.scene.config(2)
+    for N in (256, 512):
+        outs = []
+        for dev in (1, 0):
+            b, _ = make_body(pkg, po, cfg, N=N, device=dev)
+            for f in range(3):
+                b.CalculateWavesTexturesAtTime(f / 60.0)
+            outs.append((b.displacementsTextures, b.turbulenceTextures))
+            b.OnDisable()
+        assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    oceans, seeds = pkg.scene.ensemble_states(3)
+    import os
+    old = os.environ.get("OCEAN_ENSEMBLE_FUSED_INIT")
+    os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = "1"
+    try:
+        sums = []
+        for dev in (1, 0):
+            e = pkg.OceanEnsemble(256, pkg.scene.config(5)["cascades"], batch=2, device=dev)
+            sums.append(e.run(oceans, seeds, time=1.0).tolist())
+            e.close()
+        assert sums[0] == sums[1]
+    finally:
+        if old is None:
+            os.environ.pop("OCEAN_ENSEMBLE_FUSED_INIT", None)
+        else:
+            os.environ["OCEAN_ENSEMBLE_FUSED_INIT"] = old

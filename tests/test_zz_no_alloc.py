@@ -95,3 +95,32 @@ def test_noalloc_buoyancy_rejects_what_does_not_fit(pkg):
     assert lib.ocean_buoyancy_noalloc(body._h, None, 8, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.ERR_INVALID_ARGUMENT
     assert lib.ocean_buoyancy_noalloc(body._h, boxes.ctypes.data, 0, L.QUERY_NEAREST_REF, 1.0, -9.81, out.ctypes.data, 0, 0) == L.OK
     body.OnDisable()
+
+
+def test_noalloc_buoyancy_on_a_second_device(pkg):
+    """The static scratch exists once per GPU and its device address is resolved per device (cudaGetSymbolAddress with that device
+    current): an ocean on cuda:1 must get cuda:1's copy, whichever device is current in the calling thread.  Skipped on one GPU."""
+    L = pkg._lib
+    lib = L.load()
+    if lib.ocean_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cfg = pkg.scene.config(2)
+    o = cfg["ocean"]
+    bodies = []
+    for dev in (1, 0, 1):  # device 1 first: its address is resolved before device 0's
+        b = pkg.WaterBody(windSpeed=o[0], windDirection=(o[1], o[2]), gravity=o[3], fetch=o[4], depth=o[5], texturesSize=cfg["N"],
+                          cascades=cfg["cascades"], seed=77, device=dev).Awake()
+        for f in range(3):
+            b.CalculateWavesTexturesAtTime(f / 60.0)
+        bodies.append(b)
+    rng = np.random.default_rng(5)
+    boxes = _boxes(rng, 20000, cfg["N"])
+    results = []
+    for b in bodies:
+        want = b.Buoyancy(boxes, L.QUERY_BILINEAR_ALL_CASCADES)
+        got = b.BuoyancyNoAlloc(boxes, L.QUERY_BILINEAR_ALL_CASCADES)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        results.append(got)
+    assert np.array_equal(results[0], results[1]) and np.array_equal(results[0], results[2])  # same seed, same ocean on both GPUs
+    for b in bodies:
+        b.OnDisable()
